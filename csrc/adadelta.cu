@@ -1,0 +1,64 @@
+// Single-GPU fused Adadelta over the flat parameter buffer.
+//
+// torch.optim.Adadelta on CUDA runs ~12 multi-tensor kernels per step (mnist_ddp.py:73,176);
+// this is one pass: read g, v, u, p — write v, u, p (28 B/element).  The multi-GPU variant lives
+// in allreduce.cu, fused with the cross-GPU reduction.  The update follows
+// LIB:torch/optim/adadelta.py:292-302 (rho = .9, eps = 1e-6, weight_decay = 0):
+//     v   = rho v + (1-rho) g^2
+//     d   = sqrt(u + eps) / sqrt(v + eps) * g
+//     u   = rho u + (1-rho) d^2
+//     p  -= lr d
+// The last block to finish also advances the control block (step counter, sample cursor), which
+// makes this kernel the "end of step" marker inside the replayed CUDA graph.
+#include "common.cuh"
+
+__device__ __forceinline__ void adadelta_update(float g, float& p, float& v, float& u, float lr, float rho, float eps) {
+  v = fmaf(v, rho, (1.f - rho) * g * g);
+  const float d = __fdiv_rn(sqrtf(u + eps), sqrtf(v + eps)) * g;
+  u = fmaf(u, rho, (1.f - rho) * d * d);
+  p = fmaf(-lr, d, p);
+}
+
+__global__ void __launch_bounds__(256)
+adadelta_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ v, float* __restrict__ u,
+                int n4, B200Ctrl* __restrict__ ctrl, float rho, float eps, int advance_batch,
+                unsigned int* __restrict__ done_counter) {
+  const float lr = ctrl->lr;
+  for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < n4; e += gridDim.x * blockDim.x) {
+    const float4 gg = reinterpret_cast<const float4*>(g)[e];
+    float4 pp = reinterpret_cast<float4*>(p)[e], vv = reinterpret_cast<float4*>(v)[e],
+           uu = reinterpret_cast<float4*>(u)[e];
+    adadelta_update(gg.x, pp.x, vv.x, uu.x, lr, rho, eps);
+    adadelta_update(gg.y, pp.y, vv.y, uu.y, lr, rho, eps);
+    adadelta_update(gg.z, pp.z, vv.z, uu.z, lr, rho, eps);
+    adadelta_update(gg.w, pp.w, vv.w, uu.w, lr, rho, eps);
+    reinterpret_cast<float4*>(p)[e] = pp;
+    reinterpret_cast<float4*>(v)[e] = vv;
+    reinterpret_cast<float4*>(u)[e] = uu;
+  }
+  if (advance_batch >= 0 && done_counter) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      __threadfence();
+      if (atomicAdd(done_counter, 1u) == gridDim.x - 1) {  // every block has read ctrl->lr by now
+        *done_counter = 0;
+        ctrl->step += 1;
+        ctrl->pos += advance_batch;
+      }
+    }
+  }
+}
+
+// n must be a multiple of 4 (the flat layout pads every segment to 256 floats).
+// advance_batch >= 0: also advance ctrl (step += 1, pos += advance_batch); needs done_counter.
+extern "C" int b200_adadelta(float* p, const float* g, float* v, float* u, long n, void* ctrl, float rho, float eps,
+                             int advance_batch, unsigned int* done_counter, void* stream) {
+  B200_REQUIRE(n > 0 && n % 4 == 0, "adadelta: n (%ld) must be a positive multiple of 4", n);
+  const int n4 = (int)(n / 4);
+  const int grid = min(ceil_div(n4, 256), 4 * b200_sm_count());
+  adadelta_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(p, g, v, u, n4, (B200Ctrl*)ctrl, rho, eps, advance_batch,
+                                                         done_counter);
+  b200_count_launch();
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}

@@ -1,0 +1,114 @@
+// Shared device/host helpers for libb200mnist (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "../include/b200mnist.h"
+
+#define B200_CHECK(expr)                                                                  \
+  do {                                                                                    \
+    cudaError_t _e = (expr);                                                              \
+    if (_e != cudaSuccess) {                                                              \
+      b200_set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #expr, cudaGetErrorString(_e)); \
+      return B200_ERR_CUDA;                                                               \
+    }                                                                                     \
+  } while (0)
+
+#define B200_LAUNCH_CHECK() B200_CHECK(cudaGetLastError())
+
+#define B200_REQUIRE(cond, ...)        \
+  do {                                 \
+    if (!(cond)) {                     \
+      b200_set_error(__VA_ARGS__);     \
+      return B200_ERR_ARG;             \
+    }                                  \
+  } while (0)
+
+void b200_set_error(const char* fmt, ...);
+void b200_count_launch(int n = 1);
+// dst[e] = sum_p src[p*stride + e], fixed order (conv1.cu)
+void b200_launch_reduce_partials(float* dst, const float* src, int n, int nparts, int stride, cudaStream_t s);
+int b200_sm_count();
+
+// ---- model constants (mnist_ddp.py:42-47) -------------------------------------------------
+namespace net {
+constexpr int IMG = 28;
+constexpr int C1 = 32, H1 = 26, W1 = 26;   // conv1 output (NHWC)
+constexpr int C2 = 64, H2 = 24, W2 = 24;   // conv2 output before pooling
+constexpr int HP = 12, WP = 12;            // pooled
+constexpr int FC1_IN = HP * WP * C2;       // 9216, (h, w, c) order internally
+constexpr int FC1_OUT = 128;
+constexpr int NCLS = 10;
+constexpr float P_DROP1 = 0.25f, P_DROP2 = 0.5f;
+constexpr float MEAN = 0.1307f, STD = 0.3081f;
+}  // namespace net
+
+// ---- device control block: everything a replayed CUDA graph needs to read ---------------
+// One per engine, in device memory.  Kernels read it; the last kernel of a step advances it.
+struct B200Ctrl {
+  unsigned long long step;   // global optimizer step, also the dropout Philox offset
+  unsigned long long seed;   // dropout seed (same on every rank, mnist_ddp.py:140)
+  int pos;                   // first sample of this step inside the epoch's index array
+  int train;                 // bit 0: training step (backward seed is produced); bit 1: dropout active
+  float lr;                  // Adadelta lr for this epoch (StepLR applied on the host)
+  float inv_world;           // 1 / world_size
+  unsigned int epoch_flag;   // monotonically increasing cross-GPU barrier epoch
+  int reserved[3];
+};
+
+// ---- Philox4x32-10 (counter-based RNG for dropout) -------------------------------------------
+__host__ __device__ __forceinline__ uint32_t b200_mulhi(uint32_t a, uint32_t b) {
+#ifdef __CUDA_ARCH__
+  return __umulhi(a, b);
+#else
+  return (uint32_t)(((uint64_t)a * b) >> 32);
+#endif
+}
+
+__host__ __device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint2 k) {
+  const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
+#pragma unroll
+  for (int i = 0; i < 10; ++i) {
+    uint32_t hi0 = b200_mulhi(M0, c.x), lo0 = M0 * c.x;
+    uint32_t hi1 = b200_mulhi(M1, c.z), lo1 = M1 * c.z;
+    c = make_uint4(hi1 ^ c.y ^ k.x, lo1, hi0 ^ c.w ^ k.y, lo0);
+    k.x += W0;
+    k.y += W1;
+  }
+  return c;
+}
+
+// 4 random words for elements [4*e4, 4*e4+4) of dropout layer `layer` at optimizer step `step`.
+__host__ __device__ __forceinline__ uint4 dropout_bits4(unsigned long long seed, unsigned long long step,
+                                                        uint32_t layer, uint32_t e4) {
+  uint4 ctr = make_uint4(e4, layer, (uint32_t)step, (uint32_t)(step >> 32));
+  uint2 key = make_uint2((uint32_t)seed, (uint32_t)(seed >> 32));
+  return philox4x32_10(ctr, key);
+}
+
+// keep with probability 1-p: threshold = p * 2^32
+__host__ __device__ __forceinline__ bool dropout_keep(uint32_t bits, uint32_t thresh) { return bits >= thresh; }
+constexpr uint32_t DROP1_THRESH = 0x40000000u;  // p = .25
+constexpr uint32_t DROP2_THRESH = 0x80000000u;  // p = .5
+
+// ---- small device utilities -----------------------------------------------------------------
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+__device__ __forceinline__ float4 ld_nc_f4(const float* p) {
+  float4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
+  return r;
+}
+
+static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }

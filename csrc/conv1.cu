@@ -1,0 +1,162 @@
+// conv1: 1->32 channels, 3x3, stride 1, no padding (mnist_ddp.py:42,50-51).
+//
+// K = 9 is far below any tcgen05 tile, so both directions are SIMT kernels whose job is to move
+// bytes at HBM speed:
+//   forward : batch gather (index lookup into the HBM-resident uint8 dataset) + ToTensor/Normalize
+//             ((x/255 - .1307)/.3081, mnist_ddp.py:153-156) + conv + bias + ReLU, one pass, NHWC out.
+//             Replaces the reference's DataLoader worker, H2D copy, cuDNN conv, bias add and ReLU
+//             kernels.
+//   wgrad   : dW[tap][o] = sum da1 * x, db[o] = sum da1; input needs no gradient.
+#include "common.cuh"
+
+using namespace net;
+
+__device__ __forceinline__ float normalize_px(uint8_t v) {
+  // same operation order as ToTensor (div 255) then Normalize (sub mean, div std)
+  return __fdiv_rn(__fsub_rn(__fdiv_rn((float)v, 255.0f), MEAN), STD);
+}
+
+__device__ __forceinline__ int sample_of(const int32_t* __restrict__ idx, const B200Ctrl* __restrict__ ctrl, int i) {
+  int pos = ctrl->pos + i;
+  return idx ? idx[pos] : pos;
+}
+
+// grid = batch, block = 256.  Thread t: channel quad t%8, pixels t/8 + 32*k.
+__global__ void __launch_bounds__(256)
+conv1_fwd_kernel(const uint8_t* __restrict__ images, const int32_t* __restrict__ idx,
+                 const B200Ctrl* __restrict__ ctrl, const float* __restrict__ w,  // [9][32]
+                 const float* __restrict__ bias, float* __restrict__ a1) {       // [B][26][26][32]
+  __shared__ float x[IMG * IMG];
+  const int b = blockIdx.x;
+  const int sample = sample_of(idx, ctrl, b);
+  const uint8_t* src = images + (size_t)sample * (IMG * IMG);
+  if (threadIdx.x < IMG * IMG / 4) {
+    uchar4 v = reinterpret_cast<const uchar4*>(src)[threadIdx.x];
+    x[threadIdx.x * 4 + 0] = normalize_px(v.x);
+    x[threadIdx.x * 4 + 1] = normalize_px(v.y);
+    x[threadIdx.x * 4 + 2] = normalize_px(v.z);
+    x[threadIdx.x * 4 + 3] = normalize_px(v.w);
+  }
+  const int cq = threadIdx.x & 7;
+  float wr[9][4], br[4];
+#pragma unroll
+  for (int t = 0; t < 9; ++t) {
+    float4 v = *reinterpret_cast<const float4*>(w + t * C1 + cq * 4);
+    wr[t][0] = v.x; wr[t][1] = v.y; wr[t][2] = v.z; wr[t][3] = v.w;
+  }
+  {
+    float4 v = *reinterpret_cast<const float4*>(bias + cq * 4);
+    br[0] = v.x; br[1] = v.y; br[2] = v.z; br[3] = v.w;
+  }
+  __syncthreads();
+  float* out = a1 + (size_t)b * (H1 * W1 * C1);
+  for (int p = threadIdx.x >> 3; p < H1 * W1; p += 32) {
+    const int y = p / W1, xx = p - y * W1;
+    float acc[4] = {br[0], br[1], br[2], br[3]};
+#pragma unroll
+    for (int kh = 0; kh < 3; ++kh)
+#pragma unroll
+      for (int kw = 0; kw < 3; ++kw) {
+        const float v = x[(y + kh) * IMG + xx + kw];
+#pragma unroll
+        for (int c = 0; c < 4; ++c) acc[c] = fmaf(v, wr[kh * 3 + kw][c], acc[c]);
+      }
+    float4 o = make_float4(fmaxf(acc[0], 0.f), fmaxf(acc[1], 0.f), fmaxf(acc[2], 0.f), fmaxf(acc[3], 0.f));
+    *reinterpret_cast<float4*>(out + p * C1 + cq * 4) = o;
+  }
+}
+
+// grid = batch, block = 256 (8 pixel groups x 32 channels).  Writes one partial row per image:
+// part[b][0..287] = dW[tap][o], part[b][288..319] = db[o].  A fixed-order reduction follows.
+constexpr int CONV1_PART = 320;
+__global__ void __launch_bounds__(256)
+conv1_wgrad_kernel(const uint8_t* __restrict__ images, const int32_t* __restrict__ idx,
+                   const B200Ctrl* __restrict__ ctrl, const float* __restrict__ da1,  // [B][26][26][32]
+                   float* __restrict__ part) {
+  __shared__ float x[IMG * IMG];
+  __shared__ float red[8][10][C1];
+  const int b = blockIdx.x;
+  const int sample = sample_of(idx, ctrl, b);
+  const uint8_t* src = images + (size_t)sample * (IMG * IMG);
+  if (threadIdx.x < IMG * IMG / 4) {
+    uchar4 v = reinterpret_cast<const uchar4*>(src)[threadIdx.x];
+    x[threadIdx.x * 4 + 0] = normalize_px(v.x);
+    x[threadIdx.x * 4 + 1] = normalize_px(v.y);
+    x[threadIdx.x * 4 + 2] = normalize_px(v.z);
+    x[threadIdx.x * 4 + 3] = normalize_px(v.w);
+  }
+  __syncthreads();
+  const int o = threadIdx.x & 31, g = threadIdx.x >> 5;
+  const float* in = da1 + (size_t)b * (H1 * W1 * C1);
+  float acc[10];
+#pragma unroll
+  for (int t = 0; t < 10; ++t) acc[t] = 0.f;
+  for (int p = g; p < H1 * W1; p += 8) {
+    const int y = p / W1, xx = p - y * W1;
+    const float d = in[p * C1 + o];
+#pragma unroll
+    for (int kh = 0; kh < 3; ++kh)
+#pragma unroll
+      for (int kw = 0; kw < 3; ++kw) acc[kh * 3 + kw] = fmaf(d, x[(y + kh) * IMG + xx + kw], acc[kh * 3 + kw]);
+    acc[9] += d;
+  }
+#pragma unroll
+  for (int t = 0; t < 10; ++t) red[g][t][o] = acc[t];
+  __syncthreads();
+  for (int e = threadIdx.x; e < 10 * C1; e += 256) {
+    const int t = e / C1, oo = e - t * C1;
+    float s = 0.f;
+#pragma unroll
+    for (int gg = 0; gg < 8; ++gg) s += red[gg][t][oo];
+    part[(size_t)b * CONV1_PART + e] = s;  // e = t*32+o: taps first (288), then bias (32)
+  }
+}
+
+// dst[e] = sum_{p < nparts} src[p*stride + e]  — fixed order, so results are run-to-run identical.
+__global__ void reduce_partials_kernel(float* __restrict__ dst, const float* __restrict__ src, int n,
+                                       int nparts, int stride) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= n) return;
+  float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+  int p = 0;
+  for (; p + 4 <= nparts; p += 4) {
+    s0 += src[(size_t)(p + 0) * stride + e];
+    s1 += src[(size_t)(p + 1) * stride + e];
+    s2 += src[(size_t)(p + 2) * stride + e];
+    s3 += src[(size_t)(p + 3) * stride + e];
+  }
+  for (; p < nparts; ++p) s0 += src[(size_t)p * stride + e];
+  dst[e] = (s0 + s1) + (s2 + s3);
+}
+
+void b200_launch_reduce_partials(float* dst, const float* src, int n, int nparts, int stride, cudaStream_t s) {
+  reduce_partials_kernel<<<ceil_div(n, 128), 128, 0, s>>>(dst, src, n, nparts, stride);
+  b200_count_launch();
+}
+
+extern "C" int b200_conv1_fwd(const uint8_t* images, const int32_t* idx, const void* ctrl, const float* w,
+                              const float* bias, float* a1, int batch, void* stream) {
+  B200_REQUIRE(batch > 0, "conv1_fwd: batch must be > 0");
+  conv1_fwd_kernel<<<batch, 256, 0, (cudaStream_t)stream>>>(images, idx, (const B200Ctrl*)ctrl, w, bias, a1);
+  b200_count_launch();
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+extern "C" int b200_conv1_wgrad(const uint8_t* images, const int32_t* idx, const void* ctrl, const float* da1,
+                                float* part, float* dw, float* db, int batch, void* stream) {
+  B200_REQUIRE(batch > 0, "conv1_wgrad: batch must be > 0");
+  cudaStream_t s = (cudaStream_t)stream;
+  conv1_wgrad_kernel<<<batch, 256, 0, s>>>(images, idx, (const B200Ctrl*)ctrl, da1, part);
+  b200_count_launch();
+  b200_launch_reduce_partials(dw, part, 288, batch, CONV1_PART, s);
+  b200_launch_reduce_partials(db, part + 288, 32, batch, CONV1_PART, s);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+extern "C" int b200_reduce_partials(float* dst, const float* src, int n, int nparts, int stride, void* stream) {
+  b200_launch_reduce_partials(dst, src, n, nparts, stride, (cudaStream_t)stream);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}

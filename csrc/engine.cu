@@ -1,0 +1,401 @@
+// The training engine: owns device buffers, sequences the kernels of one optimizer step, and
+// replays that sequence from a CUDA graph.
+//
+// It plays the role of the reference's train()/test() loops (mnist_ddp.py:65-105) plus the
+// machinery PyTorch runs underneath them — autograd scheduling, the DataLoader/H2D path, the
+// DDP reducer hooks, the foreach optimizer — for this one static model.  The step is fully
+// device-driven: sample cursor, step counter (dropout offset), lr and the loss ring live in a
+// device control block, so the host only enqueues "one more step" and never synchronises.
+//
+// Kernel sequence of a step (single GPU, resident data):
+//   conv1_fwd (gather+normalise+conv+ReLU) -> conv2_fwd (+bias+ReLU+pool+dropout)
+//   -> fc1 GEMM (split-K) -> head_fused (reduce+bias+ReLU+dropout, fc2, log_softmax, NLL, bwd seed)
+//   -> head_wgrad -> fc1 wgrad -> fc1 dgrad (+dropout/ReLU mask) -> [bucket 0 ready]
+//   -> conv2 wgrad -> conv2 dgrad (+ReLU mask) -> conv1 wgrad -> [bucket 1 ready] -> Adadelta.
+// With world > 1 the "bucket ready" points launch the fused all-reduce+Adadelta kernels of
+// allreduce.cu on a second stream (bucket 0 overlaps the conv backward) instead of the local
+// Adadelta.  Gradients are written straight into the flat (symmetric) bucket: there is no
+// bucket copy-in/copy-out and no zero_grad (every wgrad kernel overwrites).
+#include <map>
+#include <utility>
+#include <vector>
+
+#include "common.cuh"
+#include "engine.h"
+
+using namespace net;
+
+namespace {
+
+int fc1_splits(int batch) {
+  const int tiles = ceil_div(batch, 64) * 2;
+  int s = (2 * 148 + tiles / 2) / tiles;
+  if (s < 1) s = 1;
+  if (s > 36) s = 36;
+  while (9216 % (s * 16) != 0) --s;  // equal, 16-aligned K chunks
+  return s;
+}
+
+template <class T>
+int dev_alloc(Engine* E, T** p, size_t count, bool zero = true) {
+  void* q = nullptr;
+  B200_CHECK(cudaMalloc(&q, count * sizeof(T)));
+  if (zero) B200_CHECK(cudaMemset(q, 0, count * sizeof(T)));
+  E->owned.push_back(q);
+  *p = (T*)q;
+  return B200_OK;
+}
+
+__global__ void ctrl_rewind_kernel(B200Ctrl* c) { c->pos = 0; }
+__global__ void ctrl_lr_kernel(B200Ctrl* c, float lr) { c->lr = lr; }
+__global__ void ctrl_train_kernel(B200Ctrl* c, int train) { c->train = train; }
+__global__ void zero_eval_kernel(double* acc) { acc[0] = 0.0; acc[1] = 0.0; }
+
+#define TRY(x)                    \
+  do {                            \
+    int _r = (x);                 \
+    if (_r != B200_OK) return _r; \
+  } while (0)
+
+// Forward through the head.  `ctrl` decides train/eval behaviour of the dropout epilogues.
+int enqueue_forward(Engine* E, const uint8_t* images, const uint8_t* labels, const int32_t* idx, const B200Ctrl* ctrl,
+                    int batch, bool train, cudaStream_t s) {
+  const B200EngineConfig& c = E->cfg;
+  float* P = E->P;
+  TRY(b200_conv1_fwd(images, idx, ctrl, P + c.offsets[0], P + c.offsets[1], E->a1, batch, s));
+  if (E->use_tc & B200_TC_CONV2_FWD)
+    TRY(b200_conv2_fwd_tc(E->a1, P + c.offsets[2], P + c.offsets[3], ctrl, E->pooled, E->amax, batch, s));
+  else
+    TRY(b200_conv2_fwd_simt(E->a1, P + c.offsets[2], P + c.offsets[3], ctrl, E->pooled, E->amax, batch, s));
+  const int splits = fc1_splits(batch);
+  if (E->use_tc & B200_TC_FC1_FWD)
+    TRY(b200_tc_gemm(E->pooled, P + c.offsets[4], E->fc1_part, batch, FC1_OUT, FC1_IN, 0, 0, splits, 0, nullptr, 0.f, s));
+  else
+    TRY(b200_sgemm(E->pooled, FC1_IN, 1, P + c.offsets[4], 1, FC1_IN, E->fc1_part, batch, FC1_OUT, FC1_IN, splits, 0,
+                   nullptr, 0.f, s));
+  TRY(b200_head_fused(E->fc1_part, splits, batch, P + c.offsets[5], P + c.offsets[6], P + c.offsets[7], labels, idx,
+                      ctrl, E->h, train ? E->dlogits : nullptr, train ? E->dh : nullptr, E->loss_i,
+                      train ? nullptr : E->correct_i, train ? nullptr : E->logp, s));
+  return B200_OK;
+}
+
+int enqueue_train(Engine* E, const uint8_t* images, const uint8_t* labels, const int32_t* idx, int batch,
+                  int advance, cudaStream_t s) {
+  const B200EngineConfig& c = E->cfg;
+  float* P = E->P;
+  float* G = E->G[0];
+  const float drop1_scale = E->dropout ? 1.0f / (1.0f - P_DROP1) : 1.0f;
+  TRY(enqueue_forward(E, images, labels, idx, E->ctrl, batch, true, s));
+  TRY(b200_head_wgrad(E->h, E->dlogits, E->dh, E->loss_i, batch, G + c.offsets[6], G + c.offsets[7], G + c.offsets[5],
+                      E->loss_scalar, E->ctrl, E->loss_ring, B200_LOSS_RING, s));
+  // fc1: dW1[128][9216] = dh^T . pooled ; dp = (dh . W1) * (pooled > 0 ? 1/(1-p1) : 0)
+  if (E->use_tc & B200_TC_FC1_BWD) {
+    TRY(b200_tc_gemm(E->dh, E->pooled, G + c.offsets[4], FC1_OUT, FC1_IN, batch, 1, 1, 1, 0, nullptr, 0.f, s));
+    TRY(b200_tc_gemm(E->dh, P + c.offsets[4], E->dp, batch, FC1_IN, FC1_OUT, 0, 1, 1, 1, E->pooled, drop1_scale, s));
+  } else {
+    TRY(b200_sgemm(E->dh, 1, FC1_OUT, E->pooled, FC1_IN, 1, G + c.offsets[4], FC1_OUT, FC1_IN, batch, 1, 0, nullptr,
+                   0.f, s));
+    TRY(b200_sgemm(E->dh, FC1_OUT, 1, P + c.offsets[4], FC1_IN, 1, E->dp, batch, FC1_IN, FC1_OUT, 1, 1, E->pooled,
+                   drop1_scale, s));
+  }
+  // bucket 0 (fc1.*, fc2.*) is complete here
+  if (E->hooks.bucket_ready) TRY(E->hooks.bucket_ready(E, 0, s));
+  if (E->use_tc & B200_TC_CONV2_BWD) {
+    TRY(b200_unpool_dense(E->dp, E->amax, E->dy, batch, s));
+    TRY(b200_conv2_wgrad_tc(E->dy, E->a1, E->c2_part, G + c.offsets[2], G + c.offsets[3], batch, s));
+    TRY(b200_conv2_dgrad_tc(E->dy, P + c.offsets[2], E->a1, E->da1, batch, s));
+  } else {
+    TRY(b200_conv2_wgrad_simt(E->dp, E->amax, E->a1, E->c2_part, G + c.offsets[2], G + c.offsets[3], batch, s));
+    TRY(b200_conv2_dgrad_simt(E->dp, E->amax, P + c.offsets[2], E->a1, E->da1, batch, s));
+  }
+  TRY(b200_conv1_wgrad(images, idx, E->ctrl, E->da1, E->c1_part, G + c.offsets[0], G + c.offsets[1], batch, s));
+  if (E->hooks.bucket_ready) {
+    TRY(E->hooks.bucket_ready(E, 1, s));
+    TRY(E->hooks.step_end(E, advance, s));
+  } else {
+    TRY(b200_adadelta(P, G, E->V, E->U, c.param_floats, E->ctrl, 0.9f, 1e-6f, advance, E->done_counter, s));
+  }
+  return B200_OK;
+}
+
+struct GraphKey {
+  int batch, mode;
+  bool operator<(const GraphKey& o) const { return batch != o.batch ? batch < o.batch : mode < o.mode; }
+};
+struct GraphVal {
+  cudaGraphExec_t exec;
+  int kernels;
+};
+std::map<std::pair<Engine*, GraphKey>, GraphVal> g_graphs;
+
+int run_step(Engine* E, const uint8_t* images, const uint8_t* labels, const int32_t* idx, int batch, int advance,
+             int mode, int use_graph, cudaStream_t s) {
+  if (!use_graph) return enqueue_train(E, images, labels, idx, batch, advance, s);
+  mode += E->dropout ? 0 : 8;
+  auto key = std::make_pair(E, GraphKey{batch, mode});
+  auto it = g_graphs.find(key);
+  if (it == g_graphs.end()) {
+    // First use: run once eagerly (lazy attribute set-up, tensor-map creation, error surfacing),
+    // capture on the next call.
+    if (E->warm_batches.insert({batch, mode}).second)
+      return enqueue_train(E, images, labels, idx, batch, advance, s);
+    cudaGraph_t graph = nullptr;
+    const long long before = b200_launch_count();
+    B200_CHECK(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
+    int r = enqueue_train(E, images, labels, idx, batch, advance, s);
+    cudaError_t ce = cudaStreamEndCapture(s, &graph);
+    if (r != B200_OK) {
+      if (graph) cudaGraphDestroy(graph);
+      return r;
+    }
+    B200_CHECK(ce);
+    GraphVal v{nullptr, (int)(b200_launch_count() - before)};
+    b200_count_launch(-v.kernels);  // capture did not execute anything
+    B200_CHECK(cudaGraphInstantiate(&v.exec, graph, 0));
+    cudaGraphDestroy(graph);
+    it = g_graphs.emplace(key, v).first;
+  }
+  B200_CHECK(cudaGraphLaunch(it->second.exec, s));
+  b200_count_launch(it->second.kernels);
+  return B200_OK;
+}
+
+}  // namespace
+
+extern "C" int b200_engine_create(const B200EngineConfig* cfg, void** out) {
+  B200_REQUIRE(cfg && out, "engine_create: null argument");
+  B200_REQUIRE(cfg->max_batch > 0 && cfg->param_floats > 0 && cfg->param_floats % 4 == 0,
+               "engine_create: bad max_batch/param_floats");
+  B200_CHECK(cudaSetDevice(cfg->device));
+  Engine* E = new Engine();
+  E->cfg = *cfg;
+  E->use_tc = cfg->use_tc;
+  E->nsm = b200_sm_count();
+  const size_t B = (size_t)cfg->max_batch, T = (size_t)cfg->param_floats;
+  int r = B200_OK;
+#define A(ptr, count) if (r == B200_OK) r = dev_alloc(E, &(ptr), (count))
+  if (cfg->params) E->P = cfg->params; else A(E->P, T);
+  for (int i = 0; i < 2; ++i) {
+    if (cfg->grads[i]) E->G[i] = cfg->grads[i];
+    else if (i == 0 || cfg->world > 1) { A(E->G[i], T); }
+    else E->G[i] = E->G[0];
+  }
+  if (cfg->sq_avg) E->V = cfg->sq_avg; else A(E->V, T);
+  if (cfg->acc_delta) E->U = cfg->acc_delta; else A(E->U, T);
+  for (int sp = 0; sp < 2; ++sp) {
+    const size_t n = sp == 0 ? cfg->train_n : cfg->test_n;
+    E->n[sp] = 0;
+    A(E->img[sp], n * 784 + 16);
+    A(E->lbl[sp], n + 16);
+  }
+  A(E->idx, (size_t)cfg->train_n + 16);
+  A(E->stage_img, 2 * B * 784);
+  A(E->stage_lbl, 2 * B);
+  A(E->a1, B * H1 * W1 * C1);
+  A(E->da1, B * H1 * W1 * C1);
+  A(E->pooled, B * FC1_IN);
+  A(E->dp, B * FC1_IN);
+  A(E->amax, B * FC1_IN);
+  A(E->h, B * FC1_OUT);
+  A(E->dh, B * FC1_OUT);
+  A(E->dlogits, B * 16);
+  A(E->loss_i, B);
+  A(E->correct_i, B);
+  A(E->logp, B * NCLS);
+  size_t part_cap = 0;
+  for (int b = 1; b <= cfg->max_batch; ++b) part_cap = max(part_cap, (size_t)fc1_splits(b) * b * FC1_OUT);
+  A(E->fc1_part, part_cap);
+  A(E->c1_part, B * 320);
+  A(E->c2_part, (size_t)E->nsm * (9 * C2 * C1 + C2));
+  if (cfg->use_tc & B200_TC_CONV2_BWD) A(E->dy, B * H2 * W2 * C2);
+  A(E->loss_ring, (size_t)B200_LOSS_RING);
+  A(E->loss_scalar, 4);
+  A(E->ctrl, 1);
+  A(E->ctrl_eval, 1);
+  A(E->done_counter, 4);
+  A(E->eval_acc, 2);
+#undef A
+  if (r != B200_OK) { b200_engine_destroy(E); return r; }
+  B200_CHECK(cudaMallocHost((void**)&E->h_scratch, 64));
+  const float inv_w = 1.0f / (float)(cfg->world > 0 ? cfg->world : 1);
+  TRY(b200_ctrl_set(E->ctrl, 0, cfg->seed, 0, 3, 1.0f, inv_w, nullptr));
+  TRY(b200_ctrl_set(E->ctrl_eval, 0, cfg->seed, 0, 0, 0.0f, inv_w, nullptr));
+  B200_CHECK(cudaDeviceSynchronize());
+  *out = E;
+  return B200_OK;
+}
+
+extern "C" int b200_engine_destroy(void* engine) {
+  Engine* E = (Engine*)engine;
+  if (!E) return B200_OK;
+  cudaDeviceSynchronize();
+  for (auto it = g_graphs.begin(); it != g_graphs.end();) {
+    if (it->first.first == E) { cudaGraphExecDestroy(it->second.exec); it = g_graphs.erase(it); }
+    else ++it;
+  }
+  if (E->hooks.destroy) E->hooks.destroy(E);
+  for (void* p : E->owned) cudaFree(p);
+  if (E->h_scratch) cudaFreeHost(E->h_scratch);
+  delete E;
+  return B200_OK;
+}
+
+extern "C" int b200_engine_buffer(void* engine, int which, void** ptr, size_t* bytes) {
+  Engine* E = (Engine*)engine;
+  B200_REQUIRE(E && ptr && bytes, "engine_buffer: null argument");
+  const size_t B = (size_t)E->cfg.max_batch, T = (size_t)E->cfg.param_floats;
+  switch (which) {
+    case B200_BUF_PARAMS: *ptr = E->P; *bytes = T * 4; break;
+    case B200_BUF_GRADS0: *ptr = E->G[0]; *bytes = T * 4; break;
+    case B200_BUF_GRADS1: *ptr = E->G[1]; *bytes = T * 4; break;
+    case B200_BUF_SQ_AVG: *ptr = E->V; *bytes = T * 4; break;
+    case B200_BUF_ACC_DELTA: *ptr = E->U; *bytes = T * 4; break;
+    case B200_BUF_A1: *ptr = E->a1; *bytes = B * H1 * W1 * C1 * 4; break;
+    case B200_BUF_POOLED: *ptr = E->pooled; *bytes = B * FC1_IN * 4; break;
+    case B200_BUF_AMAX: *ptr = E->amax; *bytes = B * FC1_IN; break;
+    case B200_BUF_H: *ptr = E->h; *bytes = B * FC1_OUT * 4; break;
+    case B200_BUF_DLOGITS: *ptr = E->dlogits; *bytes = B * 16 * 4; break;
+    case B200_BUF_DH: *ptr = E->dh; *bytes = B * FC1_OUT * 4; break;
+    case B200_BUF_DP: *ptr = E->dp; *bytes = B * FC1_IN * 4; break;
+    case B200_BUF_DA1: *ptr = E->da1; *bytes = B * H1 * W1 * C1 * 4; break;
+    case B200_BUF_LOSS_I: *ptr = E->loss_i; *bytes = B * 4; break;
+    case B200_BUF_LOSS_RING: *ptr = E->loss_ring; *bytes = B200_LOSS_RING * 4; break;
+    case B200_BUF_CTRL: *ptr = E->ctrl; *bytes = sizeof(B200Ctrl); break;
+    case B200_BUF_LOGP: *ptr = E->logp; *bytes = B * NCLS * 4; break;
+    case B200_BUF_STAGE_IMG: *ptr = E->stage_img; *bytes = 2 * B * 784; break;
+    case B200_BUF_STAGE_LBL: *ptr = E->stage_lbl; *bytes = 2 * B; break;
+    case B200_BUF_FC1_PART: *ptr = E->fc1_part; *bytes = 0; break;
+    default: B200_REQUIRE(false, "engine_buffer: unknown buffer id %d", which);
+  }
+  return B200_OK;
+}
+
+extern "C" int b200_engine_load_data(void* engine, int split, const uint8_t* images_host, const uint8_t* labels_host,
+                                     int n) {
+  Engine* E = (Engine*)engine;
+  B200_REQUIRE(E && (split == 0 || split == 1), "engine_load_data: bad split");
+  B200_REQUIRE(n > 0 && n <= (split == 0 ? E->cfg.train_n : E->cfg.test_n), "engine_load_data: n=%d exceeds capacity", n);
+  B200_CHECK(cudaMemcpy(E->img[split], images_host, (size_t)n * 784, cudaMemcpyHostToDevice));
+  B200_CHECK(cudaMemcpy(E->lbl[split], labels_host, (size_t)n, cudaMemcpyHostToDevice));
+  E->n[split] = n;
+  return B200_OK;
+}
+
+extern "C" int b200_engine_begin_epoch(void* engine, const int32_t* idx_host, int n, void* stream) {
+  Engine* E = (Engine*)engine;
+  cudaStream_t s = (cudaStream_t)stream;
+  B200_REQUIRE(E && n > 0 && n <= E->cfg.train_n, "engine_begin_epoch: n=%d out of range", n);
+  if (idx_host) {
+    B200_CHECK(cudaMemcpyAsync(E->idx, idx_host, (size_t)n * 4, cudaMemcpyHostToDevice, s));
+    E->idx_seq = false;
+  } else {
+    E->idx_seq = true;
+  }
+  E->epoch_n = n;
+  ctrl_rewind_kernel<<<1, 1, 0, s>>>(E->ctrl);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+extern "C" int b200_engine_set_lr(void* engine, float lr, void* stream) {
+  Engine* E = (Engine*)engine;
+  B200_REQUIRE(E, "engine_set_lr: null engine");
+  ctrl_lr_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(E->ctrl, lr);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+extern "C" int b200_engine_set_dropout(void* engine, int on, void* stream) {
+  Engine* E = (Engine*)engine;
+  B200_REQUIRE(E, "engine_set_dropout: null engine");
+  E->dropout = on != 0;
+  ctrl_train_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(E->ctrl, on ? 3 : 1);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+extern "C" int b200_engine_train_step(void* engine, int batch, int use_graph, void* stream) {
+  Engine* E = (Engine*)engine;
+  B200_REQUIRE(E && batch > 0 && batch <= E->cfg.max_batch, "engine_train_step: batch %d out of range", batch);
+  B200_REQUIRE(E->n[0] > 0, "engine_train_step: no training data loaded");
+  const int32_t* idx = E->idx_seq ? nullptr : E->idx;
+  TRY(run_step(E, E->img[0], E->lbl[0], idx, batch, batch, E->idx_seq ? 1 : 0, use_graph, (cudaStream_t)stream));
+  E->steps++;
+  return B200_OK;
+}
+
+extern "C" int b200_engine_train_step_host(void* engine, const uint8_t* images_host, const uint8_t* labels_host,
+                                           int batch, int use_graph, void* stream) {
+  Engine* E = (Engine*)engine;
+  cudaStream_t s = (cudaStream_t)stream;
+  B200_REQUIRE(E && batch > 0 && batch <= E->cfg.max_batch, "engine_train_step_host: batch %d out of range", batch);
+  const int par = (int)(E->steps & 1);
+  uint8_t* di = E->stage_img + (size_t)par * E->cfg.max_batch * 784;
+  uint8_t* dl = E->stage_lbl + (size_t)par * E->cfg.max_batch;
+  B200_CHECK(cudaMemcpyAsync(di, images_host, (size_t)batch * 784, cudaMemcpyHostToDevice, s));
+  B200_CHECK(cudaMemcpyAsync(dl, labels_host, (size_t)batch, cudaMemcpyHostToDevice, s));
+  // staged batches are addressed from sample 0: the cursor must not move (advance = 0)
+  TRY(run_step(E, di, dl, nullptr, batch, 0, 2 + par, use_graph, s));
+  E->steps++;
+  return B200_OK;
+}
+
+extern "C" int b200_engine_eval_reset(void* engine, void* stream) {
+  Engine* E = (Engine*)engine;
+  B200_REQUIRE(E, "engine_eval_reset: null engine");
+  zero_eval_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(E->eval_acc);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+extern "C" int b200_engine_eval_batch(void* engine, int split, int first, int batch, void* stream) {
+  Engine* E = (Engine*)engine;
+  cudaStream_t s = (cudaStream_t)stream;
+  B200_REQUIRE(E && (split == 0 || split == 1), "engine_eval_batch: bad split");
+  B200_REQUIRE(batch > 0 && batch <= E->cfg.max_batch && first >= 0 && first + batch <= E->n[split],
+               "engine_eval_batch: range [%d, %d) outside split of %d samples (max batch %d)", first, first + batch,
+               E->n[split], E->cfg.max_batch);
+  TRY(b200_ctrl_set(E->ctrl_eval, 0, E->cfg.seed, first, 0, 0.f, 1.f, s));
+  TRY(enqueue_forward(E, E->img[split], E->lbl[split], nullptr, E->ctrl_eval, batch, false, s));
+  TRY(b200_eval_accumulate(E->loss_i, E->correct_i, batch, E->eval_acc, s));
+  return B200_OK;
+}
+
+extern "C" int b200_engine_eval_result(void* engine, double* nll_sum_host, long long* correct_host, void* stream) {
+  Engine* E = (Engine*)engine;
+  cudaStream_t s = (cudaStream_t)stream;
+  B200_REQUIRE(E && nll_sum_host && correct_host, "engine_eval_result: null argument");
+  double* hs = (double*)E->h_scratch;
+  B200_CHECK(cudaMemcpyAsync(hs, E->eval_acc, 16, cudaMemcpyDeviceToHost, s));
+  B200_CHECK(cudaStreamSynchronize(s));
+  *nll_sum_host = hs[0];
+  *correct_host = (long long)(hs[1] + 0.5);
+  return B200_OK;
+}
+
+extern "C" int b200_engine_read_loss(void* engine, unsigned long long step, float* loss_host, void* stream) {
+  Engine* E = (Engine*)engine;
+  cudaStream_t s = (cudaStream_t)stream;
+  B200_REQUIRE(E && loss_host, "engine_read_loss: null argument");
+  float* hs = (float*)E->h_scratch + 8;
+  B200_CHECK(cudaMemcpyAsync(hs, E->loss_ring + (step % B200_LOSS_RING), 4, cudaMemcpyDeviceToHost, s));
+  B200_CHECK(cudaStreamSynchronize(s));
+  *loss_host = *hs;
+  return B200_OK;
+}
+
+extern "C" int b200_engine_step_count(void* engine, unsigned long long* steps_host) {
+  Engine* E = (Engine*)engine;
+  B200_REQUIRE(E && steps_host, "engine_step_count: null argument");
+  *steps_host = E->steps;
+  return B200_OK;
+}
+
+extern "C" int b200_engine_launches_per_step(void* engine, int batch, int* n_host) {
+  Engine* E = (Engine*)engine;
+  B200_REQUIRE(E && n_host, "engine_launches_per_step: null argument");
+  *n_host = -1;
+  for (auto& kv : g_graphs)
+    if (kv.first.first == E && kv.first.second.batch == batch) *n_host = kv.second.kernels;
+  return B200_OK;
+}

@@ -1,0 +1,45 @@
+// Engine state shared between engine.cu (step sequencing) and allreduce.cu (data-parallel hooks).
+#pragma once
+#include <set>
+#include <utility>
+#include <vector>
+
+#include "common.cuh"
+
+enum { B200_TC_CONV2_FWD = 1, B200_TC_FC1_FWD = 2, B200_TC_FC1_BWD = 4, B200_TC_CONV2_BWD = 8 };
+
+struct Engine;
+struct EngineHooks {
+  // called (inside the step's stream order / graph capture) when a gradient bucket is complete
+  int (*bucket_ready)(Engine*, int bucket, cudaStream_t) = nullptr;
+  // called once per step after the last bucket: joins side streams, advances the control block
+  int (*step_end)(Engine*, int advance, cudaStream_t) = nullptr;
+  void (*destroy)(Engine*) = nullptr;
+  void* state = nullptr;
+};
+
+struct Engine {
+  B200EngineConfig cfg{};
+  int use_tc = 0, nsm = 148;
+  std::vector<void*> owned;
+  float *P = nullptr, *G[2] = {nullptr, nullptr}, *V = nullptr, *U = nullptr;
+  uint8_t *img[2] = {nullptr, nullptr}, *lbl[2] = {nullptr, nullptr};
+  int n[2] = {0, 0};
+  int32_t* idx = nullptr;
+  bool idx_seq = true;
+  int epoch_n = 0;
+  uint8_t *stage_img = nullptr, *stage_lbl = nullptr;
+  float *a1 = nullptr, *da1 = nullptr, *pooled = nullptr, *dp = nullptr, *h = nullptr, *dh = nullptr,
+        *dlogits = nullptr, *loss_i = nullptr, *logp = nullptr, *fc1_part = nullptr, *c1_part = nullptr,
+        *c2_part = nullptr, *dy = nullptr, *loss_ring = nullptr, *loss_scalar = nullptr;
+  uint8_t* amax = nullptr;
+  int* correct_i = nullptr;
+  B200Ctrl *ctrl = nullptr, *ctrl_eval = nullptr;
+  unsigned int* done_counter = nullptr;
+  double* eval_acc = nullptr;
+  void* h_scratch = nullptr;  // 64 B pinned
+  unsigned long long steps = 0;
+  bool dropout = true;  // false: train without dropout (numerics / DDP-equivalence tests)
+  std::set<std::pair<int, int>> warm_batches;  // (batch, mode) pairs that already ran eagerly once
+  EngineHooks hooks;
+};

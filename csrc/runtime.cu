@@ -1,0 +1,54 @@
+// Process-wide runtime state of libb200mnist: error strings, launch accounting, device facts.
+#include <atomic>
+#include <cstdarg>
+#include <cstring>
+
+#include "common.cuh"
+
+static thread_local char g_err[1024] = "";
+static std::atomic<long long> g_launches{0};
+
+void b200_set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+void b200_count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+
+int b200_sm_count() {
+  static int cached[64] = {0};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= 64) return 148;
+  if (!cached[dev]) {
+    int n = 0;
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    cached[dev] = n > 0 ? n : 148;
+  }
+  return cached[dev];
+}
+
+__global__ void ctrl_set_kernel(B200Ctrl* c, unsigned long long step, unsigned long long seed, int pos, int train,
+                                float lr, float inv_world) {
+  c->step = step;
+  c->seed = seed;
+  c->pos = pos;
+  c->train = train;
+  c->lr = lr;
+  c->inv_world = inv_world;
+}
+
+extern "C" const char* b200_last_error(void) { return g_err; }
+extern "C" int b200_version(void) { return 100; }
+extern "C" long long b200_launch_count(void) { return g_launches.load(); }
+extern "C" int b200_ctrl_bytes(void) { return (int)sizeof(B200Ctrl); }
+
+extern "C" int b200_ctrl_set(void* ctrl, unsigned long long step, unsigned long long seed, int pos, int train,
+                             float lr, float inv_world, void* stream) {
+  B200_REQUIRE(ctrl != nullptr, "ctrl_set: null ctrl");
+  ctrl_set_kernel<<<1, 1, 0, (cudaStream_t)stream>>>((B200Ctrl*)ctrl, step, seed, pos, train, lr, inv_world);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}

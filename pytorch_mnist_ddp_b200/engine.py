@@ -1,0 +1,246 @@
+"""Python face of the native training engine (csrc/engine.cu) and the B200 trainer backend.
+
+`NativeEngine` is a thin ctypes wrapper: it owns an engine handle, exposes the engine's device
+buffers as zero-copy ``torch`` tensors (``__cuda_array_interface__``), and forwards
+``train_step`` / ``eval`` calls on torch's current CUDA stream.  `B200Backend` adapts it to the
+epoch driver in trainer.py, i.e. it is what ``mnist.py`` / ``mnist_ddp.py`` run on a GPU.
+
+Reference call sites replaced: train() body mnist_ddp.py:67-73, test() body mnist_ddp.py:93-99,
+``Net().to(device)`` :170, ``optim.Adadelta`` :176, the DDP wrap :173 (see parallel/fused_ddp.py).
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from typing import Dict, Optional, Tuple
+
+import torch
+
+from . import _native as N
+from .models.net import Net, ParamLayout
+from .parallel.dist import DistInfo
+from .utils.data import MnistSplit
+
+# buffer ids (include/b200mnist.h)
+(BUF_PARAMS, BUF_GRADS0, BUF_GRADS1, BUF_SQ_AVG, BUF_ACC_DELTA, BUF_A1, BUF_POOLED, BUF_AMAX, BUF_H,
+ BUF_DLOGITS, BUF_DH, BUF_DP, BUF_DA1, BUF_LOSS_I, BUF_LOSS_RING, BUF_CTRL, BUF_LOGP, BUF_STAGE_IMG,
+ BUF_STAGE_LBL, BUF_FC1_PART) = range(20)
+LOSS_RING = 1024
+TC_CONV2_FWD, TC_FC1_FWD, TC_FC1_BWD, TC_CONV2_BWD = 1, 2, 4, 8
+TC_ALL = 15
+
+
+def default_tc_mask() -> int:
+    """Which layers run on tcgen05 tensor cores (bit mask); B200_TC=0 forces CUDA cores."""
+    env = os.environ.get("B200_TC")
+    if env is not None:
+        return int(env, 0)
+    return DEFAULT_TC
+
+
+DEFAULT_TC = 0
+
+
+class _DevArray:
+    def __init__(self, ptr: int, shape: Tuple[int, ...], typestr: str) -> None:
+        self.__cuda_array_interface__ = {"shape": shape, "typestr": typestr, "data": (ptr, False),
+                                         "version": 2, "strides": None}
+
+
+_TYPESTR = {torch.float32: ("<f4", 4), torch.uint8: ("|u1", 1), torch.int32: ("<i4", 4), torch.float64: ("<f8", 8)}
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+class NativeEngine:
+    def __init__(self, max_batch: int, train_n: int, test_n: int, seed: int = 1, world: int = 1, rank: int = 0,
+                 use_tc: Optional[int] = None, device: Optional[int] = None,
+                 external: Optional[Dict[str, int]] = None) -> None:
+        if not torch.cuda.is_available():
+            raise N.NativeError("the native engine needs a CUDA device")
+        self.lib = N.lib()
+        self.layout = ParamLayout()
+        self.device = torch.cuda.current_device() if device is None else device
+        self.max_batch, self.world, self.rank = max_batch, world, rank
+        cfg = N.EngineConfig()
+        cfg.device, cfg.max_batch, cfg.world, cfg.rank, cfg.seed = self.device, max_batch, world, rank, seed
+        cfg.use_tc = default_tc_mask() if use_tc is None else use_tc
+        cfg.train_n, cfg.test_n, cfg.param_floats = train_n, test_n, self.layout.total
+        for i, o in enumerate(self.layout.offsets()):
+            cfg.offsets[i] = o
+        for b, (s, e) in enumerate(self.layout.bucket_ranges):
+            cfg.bucket_begin[b], cfg.bucket_end[b] = s, e
+        ext = external or {}
+        cfg.params = ext.get("params")
+        cfg.grads[0], cfg.grads[1] = ext.get("grads0"), ext.get("grads1")
+        cfg.sq_avg, cfg.acc_delta = ext.get("sq_avg"), ext.get("acc_delta")
+        self.use_tc = cfg.use_tc
+        self._cfg = cfg
+        h = ctypes.c_void_p()
+        N.check(self.lib.b200_engine_create(ctypes.byref(cfg), ctypes.byref(h)))
+        self.handle = h
+        self._keep = []
+        self.params = self.buffer(BUF_PARAMS, torch.float32)
+        self.grads = self.buffer(BUF_GRADS0, torch.float32)
+        self.sq_avg = self.buffer(BUF_SQ_AVG, torch.float32)
+        self.acc_delta = self.buffer(BUF_ACC_DELTA, torch.float32)
+        self.loss_ring = self.buffer(BUF_LOSS_RING, torch.float32)
+        self.steps = 0
+
+    # ---- plumbing
+    def buffer(self, which: int, dtype: torch.dtype, shape: Optional[Tuple[int, ...]] = None) -> torch.Tensor:
+        p, nb = ctypes.c_void_p(), ctypes.c_size_t()
+        N.check(self.lib.b200_engine_buffer(self.handle, which, ctypes.byref(p), ctypes.byref(nb)))
+        ts, isz = _TYPESTR[dtype]
+        if shape is None:
+            shape = (nb.value // isz,)
+        return torch.as_tensor(_DevArray(p.value, shape, ts), device=f"cuda:{self.device}")
+
+    def close(self) -> None:
+        if getattr(self, "handle", None):
+            self.lib.b200_engine_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self) -> None:  # pragma: no cover
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- data / parameters
+    def load_data(self, split: int, data: MnistSplit) -> None:
+        img = data.images.contiguous()
+        lbl = data.labels.contiguous()
+        N.check(self.lib.b200_engine_load_data(self.handle, split, img.data_ptr(), lbl.data_ptr(), len(data)))
+
+    def set_state_dict(self, state: Dict[str, torch.Tensor]) -> None:
+        self.params.copy_(self.layout.pack(state).to(self.params.device))
+
+    def state_dict(self, prefix: str = "") -> Dict[str, torch.Tensor]:
+        return self.layout.unpack(self.params, prefix)
+
+    def grad_dict(self) -> Dict[str, torch.Tensor]:
+        return self.layout.unpack(self.grads)
+
+    # ---- training
+    def begin_epoch(self, idx: Optional[torch.Tensor]) -> None:
+        if idx is None:
+            N.check(self.lib.b200_engine_begin_epoch(self.handle, None, self._cfg.train_n, _stream()))
+            return
+        pinned = idx.to(torch.int32).contiguous().pin_memory()
+        self._keep = [pinned]  # must outlive the async copy
+        N.check(self.lib.b200_engine_begin_epoch(self.handle, pinned.data_ptr(), pinned.numel(), _stream()))
+
+    def set_lr(self, lr: float) -> None:
+        N.check(self.lib.b200_engine_set_lr(self.handle, float(lr), _stream()))
+
+    def set_dropout(self, on: bool) -> None:
+        N.check(self.lib.b200_engine_set_dropout(self.handle, int(on), _stream()))
+
+    def train_step(self, batch: int, use_graph: bool = True) -> int:
+        N.check(self.lib.b200_engine_train_step(self.handle, batch, int(use_graph), _stream()))
+        self.steps += 1
+        return self.steps - 1
+
+    def train_step_host(self, images_u8: torch.Tensor, labels_u8: torch.Tensor, use_graph: bool = True) -> int:
+        """Public streaming API: the batch is copied from (pinned) host memory every step."""
+        b = int(images_u8.shape[0])
+        N.check(self.lib.b200_engine_train_step_host(self.handle, images_u8.data_ptr(), labels_u8.data_ptr(), b,
+                                                     int(use_graph), _stream()))
+        self.steps += 1
+        return self.steps - 1
+
+    def read_loss(self, step: int) -> float:
+        out = ctypes.c_float()
+        N.check(self.lib.b200_engine_read_loss(self.handle, step, ctypes.byref(out), _stream()))
+        return float(out.value)
+
+    def launches_per_step(self, batch: int) -> int:
+        n = ctypes.c_int()
+        N.check(self.lib.b200_engine_launches_per_step(self.handle, batch, ctypes.byref(n)))
+        return int(n.value)
+
+    # ---- evaluation
+    def evaluate(self, split: int, n: int, batch: int) -> Tuple[float, int]:
+        s = _stream()
+        N.check(self.lib.b200_engine_eval_reset(self.handle, s))
+        for first in range(0, n, batch):
+            N.check(self.lib.b200_engine_eval_batch(self.handle, split, first, min(batch, n - first), s))
+        nll, correct = ctypes.c_double(), ctypes.c_longlong()
+        N.check(self.lib.b200_engine_eval_result(self.handle, ctypes.byref(nll), ctypes.byref(correct), s))
+        return float(nll.value), int(correct.value)
+
+    def forward_logp(self, split: int, first: int, batch: int) -> torch.Tensor:
+        """Eval-mode log-probabilities of `batch` samples of a split (for tests / inference)."""
+        N.check(self.lib.b200_engine_eval_batch(self.handle, split, first, batch, _stream()))
+        return self.buffer(BUF_LOGP, torch.float32)[: batch * 10].view(batch, 10).clone()
+
+
+class B200Backend:
+    """trainer.fit() backend running on the native engine (one process = one GPU)."""
+
+    name = "b200"
+
+    def __init__(self, train: MnistSplit, test: MnistSplit, info: DistInfo, lr: float, seed: int = 1,
+                 comm: str = "auto", use_graph: bool = True, max_batch: int = 4096) -> None:
+        self.info = info
+        self.use_graph = use_graph
+        self.train_split, self.test_split = train, test
+        world = info.world_size if info.distributed else 1
+        model = Net()  # CPU construction right after manual_seed: reference init stream
+        self.ddp = None
+        external = None
+        if info.distributed and world > 1:
+            from .parallel.fused_ddp import FusedDataParallel
+            self.ddp = FusedDataParallel(info, comm=comm)
+            external = self.ddp.allocate(ParamLayout().total)
+        self.engine = NativeEngine(max_batch, len(train), len(test), seed=seed, world=world, rank=info.rank,
+                                   external=external)
+        self.engine.load_data(0, train)
+        self.engine.load_data(1, test)
+        self.engine.set_state_dict(model.state_dict())
+        if self.ddp is not None:
+            self.ddp.attach(self.engine)  # broadcasts rank 0's parameters, installs the bucket hooks
+        self.engine.set_lr(lr)
+        self._pinned_loss = torch.empty(64, dtype=torch.float32).pin_memory()
+        self._slot = 0
+
+    def begin_epoch(self, indices: torch.Tensor) -> None:
+        self._epoch_n = int(indices.numel())
+        self.engine.begin_epoch(indices)
+
+    def train_step(self, step: int, batch: int, want_loss: bool = True):
+        bsz = min(batch, self._epoch_n - step * batch)
+        s = self.engine.train_step(bsz, self.use_graph)
+        if not want_loss:
+            return None
+        slot = self._slot
+        self._slot = (self._slot + 1) % 64
+        self._pinned_loss[slot: slot + 1].copy_(self.engine.loss_ring[s % LOSS_RING: s % LOSS_RING + 1],
+                                                non_blocking=True)
+        ev = torch.cuda.Event()
+        ev.record()
+        return (slot, ev)
+
+    def loss(self, token) -> float:
+        slot, ev = token
+        ev.synchronize()
+        return float(self._pinned_loss[slot])
+
+    def evaluate(self, split: MnistSplit, batch: int) -> Tuple[float, int]:
+        which = 1 if split is self.test_split else 0
+        return self.engine.evaluate(which, len(split), min(batch, self.engine.max_batch))
+
+    def set_lr(self, lr: float) -> None:
+        self.engine.set_lr(lr)
+
+    def state_dict(self) -> Dict[str, torch.Tensor]:
+        return self.engine.state_dict()
+
+    def load_state_dict(self, state: Dict[str, torch.Tensor]) -> None:
+        self.engine.set_state_dict(state)
+
+    def finish(self) -> None:
+        torch.cuda.synchronize()

@@ -1,0 +1,201 @@
+"""End-to-end numerics of the native engine against the PyTorch model it replaces.
+
+One full optimizer step (forward, backward, Adadelta) with dropout disabled must reproduce
+torch's loss, every gradient and every updated parameter; with dropout enabled the run must be
+statistically sane and deterministic for a fixed seed.  Also covers eval, the streaming
+(host-batch) entry point, CUDA-graph replay vs eager launch, and checkpoint round-trips.
+"""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module", autouse=True)
+def _fp32_oracle():
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    yield
+
+
+def _data(n_train=1024, n_test=512):
+    from pytorch_mnist_ddp_b200.utils.data import synthetic_split
+    return synthetic_split(True, n_train), synthetic_split(False, n_test)
+
+
+def _engine(train, test, max_batch=256, use_tc=0, seed=1):
+    from pytorch_mnist_ddp_b200.engine import NativeEngine
+    from pytorch_mnist_ddp_b200.models.net import Net
+    torch.manual_seed(seed)
+    net = Net()
+    eng = NativeEngine(max_batch, len(train), len(test), seed=seed, use_tc=use_tc)
+    eng.load_data(0, train)
+    eng.load_data(1, test)
+    eng.set_state_dict(net.state_dict())
+    return eng, net.cuda()
+
+
+def _norm(u8):
+    return (((u8.float() / 255) - 0.1307) / 0.3081).unsqueeze(1)
+
+
+def _tc_masks():
+    from pytorch_mnist_ddp_b200 import _native as N
+    return [0, 15] if N.lib().b200_has_tc() else [0]
+
+
+@pytest.mark.parametrize("use_tc", [0, 15])
+@pytest.mark.parametrize("batch", [64, 200])
+def test_train_step_matches_torch_without_dropout(use_tc, batch):
+    if use_tc not in _tc_masks():
+        pytest.skip("tensor-core kernels not built")
+    train, test = _data()
+    eng, net = _engine(train, test, use_tc=use_tc)
+    eng.set_dropout(False)
+    net.eval()  # dropout off, gradients still flow
+    opt = torch.optim.Adadelta(net.parameters(), lr=1.0)
+    idx = torch.randperm(len(train))[: 3 * batch].to(torch.int32)
+    eng.begin_epoch(idx)
+    tol_g = dict(rtol=5e-2, atol=2e-3) if use_tc else dict(rtol=2e-3, atol=2e-5)
+    for step in range(3):
+        sel = idx[step * batch: (step + 1) * batch].long()
+        x, y = _norm(train.images[sel]).cuda(), train.labels[sel].long().cuda()
+        opt.zero_grad()
+        loss = F.nll_loss(net(x), y)
+        loss.backward()
+        s = eng.train_step(batch, use_graph=False)
+        got = eng.read_loss(s)
+        assert abs(got - loss.item()) < (5e-3 if use_tc else 2e-4), (step, got, loss.item())
+        if step == 0:
+            grads = eng.grad_dict()
+            for name, p in net.named_parameters():
+                g = grads[name].cuda()
+                scale = p.grad.abs().max().item()
+                torch.testing.assert_close(g, p.grad, rtol=tol_g["rtol"], atol=tol_g["atol"] * max(scale, 1e-3) * 50,
+                                           msg=lambda m, n=name: f"{n}: {m}")
+        opt.step()
+        if not use_tc:
+            sd = eng.state_dict()
+            for name, p in net.named_parameters():
+                torch.testing.assert_close(sd[name].cuda(), p.detach(), rtol=1e-3, atol=2e-4,
+                                           msg=lambda m, n=name: f"{n} after step {step}: {m}")
+    eng.close()
+
+
+def test_graph_replay_equals_eager():
+    train, test = _data()
+    results = []
+    for use_graph in (False, True):
+        eng, _ = _engine(train, test)
+        eng.begin_epoch(torch.arange(640, dtype=torch.int32))
+        for _ in range(10):
+            eng.train_step(64, use_graph=use_graph)
+        torch.cuda.synchronize()
+        results.append((eng.params.clone(), eng.loss_ring[:10].clone()))
+        if use_graph:
+            assert eng.launches_per_step(64) > 0
+        eng.close()
+    assert torch.equal(results[0][0], results[1][0]), "graph replay must be bit-identical to eager launches"
+    assert torch.equal(results[0][1], results[1][1])
+
+
+def test_training_reduces_loss_on_learnable_data():
+    # labels = a deterministic function of the image -> the net can fit it; loss must fall
+    from pytorch_mnist_ddp_b200.utils.data import MnistSplit
+    g = torch.Generator().manual_seed(0)
+    labels = torch.randint(0, 10, (2048,), generator=g, dtype=torch.uint8)
+    protos = torch.randint(0, 256, (10, 28, 28), generator=g, dtype=torch.uint8)
+    noise = torch.randint(0, 64, (2048, 28, 28), generator=g, dtype=torch.uint8)
+    images = (protos[labels.long()] // 2 + noise).to(torch.uint8)
+    train = MnistSplit(images, labels, True)
+    test = MnistSplit(images[:512].clone(), labels[:512].clone(), True)
+    eng, _ = _engine(train, test)
+    first = last = None
+    for epoch in range(3):
+        eng.begin_epoch(torch.randperm(2048).to(torch.int32))
+        for i in range(2048 // 128):
+            s = eng.train_step(128)
+            if first is None:
+                first = eng.read_loss(s)
+    last = eng.read_loss(s)
+    nll, correct = eng.evaluate(1, 512, 256)
+    assert last < 0.5 * first, (first, last)
+    assert correct > 400, correct
+    eng.close()
+
+
+def test_eval_matches_torch():
+    train, test = _data()
+    eng, net = _engine(train, test)
+    net.eval()
+    nll, correct = eng.evaluate(1, len(test), 200)  # ragged last batch (512 = 2*200 + 112)
+    with torch.no_grad():
+        out = net(_norm(test.images).cuda())
+        y = test.labels.long().cuda()
+        ref_nll = F.nll_loss(out, y, reduction="sum").item()
+        ref_correct = out.argmax(1).eq(y).sum().item()
+    assert abs(nll - ref_nll) < 1e-2 * max(1.0, abs(ref_nll)) * 1e-1
+    assert abs(correct - ref_correct) <= 2
+    lp = eng.forward_logp(1, 0, 64)
+    torch.testing.assert_close(lp, out[:64], rtol=1e-3, atol=1e-3)
+    eng.close()
+
+
+def test_host_batch_step_equals_resident_step():
+    train, test = _data()
+    a, _ = _engine(train, test)
+    b, _ = _engine(train, test)
+    idx = torch.randperm(len(train))[:256]
+    a.begin_epoch(idx.to(torch.int32))
+    b.begin_epoch(None)
+    for step in range(4):
+        sel = idx[step * 64: (step + 1) * 64]
+        a.train_step(64)
+        imgs = train.images[sel].contiguous().pin_memory()
+        lbls = train.labels[sel].contiguous().pin_memory()
+        b.train_step_host(imgs, lbls)
+        torch.cuda.synchronize()
+    assert torch.equal(a.params, b.params)
+    a.close(); b.close()
+
+
+def test_dropout_is_deterministic_per_seed_and_differs_across_seeds():
+    train, test = _data()
+    outs = []
+    for seed in (1, 1, 2):
+        torch.manual_seed(0)
+        from pytorch_mnist_ddp_b200.engine import NativeEngine
+        from pytorch_mnist_ddp_b200.models.net import Net
+        net = Net()
+        eng = NativeEngine(256, len(train), len(test), seed=seed, use_tc=0)
+        eng.load_data(0, train); eng.load_data(1, test)
+        eng.set_state_dict(net.state_dict())
+        eng.begin_epoch(None)
+        for _ in range(3):
+            eng.train_step(64)
+        torch.cuda.synchronize()
+        outs.append(eng.params.clone())
+        eng.close()
+    assert torch.equal(outs[0], outs[1])
+    assert not torch.equal(outs[0], outs[2])
+
+
+def test_checkpoint_roundtrip_through_reference_format(tmp_path):
+    from pytorch_mnist_ddp_b200.models.net import Net
+    from pytorch_mnist_ddp_b200.utils import checkpoint
+    train, test = _data()
+    eng, _ = _engine(train, test)
+    eng.begin_epoch(None)
+    eng.train_step(64)
+    path = str(tmp_path / "mnist_cnn.pt")
+    checkpoint.save(eng.state_dict(), path, prefix="module.")
+    raw = torch.load(path, weights_only=True)
+    assert list(raw)[0] == "module.conv1.weight" and raw["module.fc1.weight"].shape == (128, 9216)
+    net = Net()
+    net.load_state_dict(checkpoint.load(path))  # loads into the reference architecture
+    net = net.cuda().eval()
+    with torch.no_grad():
+        ref = net(_norm(test.images[:32]).cuda())
+    torch.testing.assert_close(eng.forward_logp(1, 0, 32), ref, rtol=1e-3, atol=1e-3)
+    eng.close()
