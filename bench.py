@@ -120,6 +120,7 @@ def run_ours(args) -> dict:
     train, test = synthetic_split(True), synthetic_split(False, 1000)
     backend = B200Backend(train, test, info, lr=1.0, seed=1, comm=args.comm, max_batch=max(args.batch, 1000))
     eng = backend.engine
+    torch.cuda.set_stream(eng.stream)  # events, flushes and copies below are ordered with the engine
     B, K, W = args.batch, args.steps, args.warmup
     per_rank = len(train) // world
     steps_per_epoch = per_rank // B

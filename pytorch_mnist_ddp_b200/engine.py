@@ -2,8 +2,11 @@
 
 `NativeEngine` is a thin ctypes wrapper: it owns an engine handle, exposes the engine's device
 buffers as zero-copy ``torch`` tensors (``__cuda_array_interface__``), and forwards
-``train_step`` / ``eval`` calls on torch's current CUDA stream.  `B200Backend` adapts it to the
-epoch driver in trainer.py, i.e. it is what ``mnist.py`` / ``mnist_ddp.py`` run on a GPU.
+``train_step`` / ``eval`` calls.  All engine work is enqueued on ONE dedicated CUDA stream
+(``engine.stream``; the legacy default stream cannot be graph-captured); helper methods that mix
+torch ops with engine buffers run those ops on the same stream, and every method that hands data
+back to the caller synchronises that stream first.  `B200Backend` adapts the engine to the epoch
+driver in trainer.py, i.e. it is what ``mnist.py`` / ``mnist_ddp.py`` run on a GPU.
 
 Reference call sites replaced: train() body mnist_ddp.py:67-73, test() body mnist_ddp.py:93-99,
 ``Net().to(device)`` :170, ``optim.Adadelta`` :176, the DDP wrap :173 (see parallel/fused_ddp.py).
@@ -28,6 +31,7 @@ from .utils.data import MnistSplit
 LOSS_RING = 1024
 TC_CONV2_FWD, TC_FC1_FWD, TC_FC1_BWD, TC_CONV2_BWD = 1, 2, 4, 8
 TC_ALL = 15
+DEFAULT_TC = 0
 
 
 def default_tc_mask() -> int:
@@ -35,10 +39,7 @@ def default_tc_mask() -> int:
     env = os.environ.get("B200_TC")
     if env is not None:
         return int(env, 0)
-    return DEFAULT_TC
-
-
-DEFAULT_TC = 0
+    return DEFAULT_TC if N.lib().b200_has_tc() else 0
 
 
 class _DevArray:
@@ -50,10 +51,6 @@ class _DevArray:
 _TYPESTR = {torch.float32: ("<f4", 4), torch.uint8: ("|u1", 1), torch.int32: ("<i4", 4), torch.float64: ("<f8", 8)}
 
 
-def _stream() -> int:
-    return torch.cuda.current_stream().cuda_stream
-
-
 class NativeEngine:
     def __init__(self, max_batch: int, train_n: int, test_n: int, seed: int = 1, world: int = 1, rank: int = 0,
                  use_tc: Optional[int] = None, device: Optional[int] = None,
@@ -63,6 +60,7 @@ class NativeEngine:
         self.lib = N.lib()
         self.layout = ParamLayout()
         self.device = torch.cuda.current_device() if device is None else device
+        self.stream = torch.cuda.Stream(device=self.device)
         self.max_batch, self.world, self.rank = max_batch, world, rank
         cfg = N.EngineConfig()
         cfg.device, cfg.max_batch, cfg.world, cfg.rank, cfg.seed = self.device, max_batch, world, rank, seed
@@ -79,6 +77,7 @@ class NativeEngine:
         self.use_tc = cfg.use_tc
         self._cfg = cfg
         h = ctypes.c_void_p()
+        torch.cuda.synchronize(self.device)
         N.check(self.lib.b200_engine_create(ctypes.byref(cfg), ctypes.byref(h)))
         self.handle = h
         self._keep = []
@@ -90,6 +89,16 @@ class NativeEngine:
         self.steps = 0
 
     # ---- plumbing
+    def _s(self) -> int:
+        return self.stream.cuda_stream
+
+    def on_stream(self):
+        """Context manager: torch ops inside are ordered with the engine's work."""
+        return torch.cuda.stream(self.stream)
+
+    def synchronize(self) -> None:
+        self.stream.synchronize()
+
     def buffer(self, which: int, dtype: torch.dtype, shape: Optional[Tuple[int, ...]] = None) -> torch.Tensor:
         p, nb = ctypes.c_void_p(), ctypes.c_size_t()
         N.check(self.lib.b200_engine_buffer(self.handle, which, ctypes.byref(p), ctypes.byref(nb)))
@@ -116,31 +125,36 @@ class NativeEngine:
         N.check(self.lib.b200_engine_load_data(self.handle, split, img.data_ptr(), lbl.data_ptr(), len(data)))
 
     def set_state_dict(self, state: Dict[str, torch.Tensor]) -> None:
-        self.params.copy_(self.layout.pack(state).to(self.params.device))
+        flat = self.layout.pack(state).pin_memory()
+        with self.on_stream():
+            self.params.copy_(flat, non_blocking=True)
+        self.synchronize()
 
     def state_dict(self, prefix: str = "") -> Dict[str, torch.Tensor]:
+        self.synchronize()
         return self.layout.unpack(self.params, prefix)
 
     def grad_dict(self) -> Dict[str, torch.Tensor]:
+        self.synchronize()
         return self.layout.unpack(self.grads)
 
     # ---- training
     def begin_epoch(self, idx: Optional[torch.Tensor]) -> None:
         if idx is None:
-            N.check(self.lib.b200_engine_begin_epoch(self.handle, None, self._cfg.train_n, _stream()))
+            N.check(self.lib.b200_engine_begin_epoch(self.handle, None, self._cfg.train_n, self._s()))
             return
         pinned = idx.to(torch.int32).contiguous().pin_memory()
-        self._keep = [pinned]  # must outlive the async copy
-        N.check(self.lib.b200_engine_begin_epoch(self.handle, pinned.data_ptr(), pinned.numel(), _stream()))
+        self._keep = (self._keep + [pinned])[-2:]  # must outlive the async copy
+        N.check(self.lib.b200_engine_begin_epoch(self.handle, pinned.data_ptr(), pinned.numel(), self._s()))
 
     def set_lr(self, lr: float) -> None:
-        N.check(self.lib.b200_engine_set_lr(self.handle, float(lr), _stream()))
+        N.check(self.lib.b200_engine_set_lr(self.handle, float(lr), self._s()))
 
     def set_dropout(self, on: bool) -> None:
-        N.check(self.lib.b200_engine_set_dropout(self.handle, int(on), _stream()))
+        N.check(self.lib.b200_engine_set_dropout(self.handle, int(on), self._s()))
 
     def train_step(self, batch: int, use_graph: bool = True) -> int:
-        N.check(self.lib.b200_engine_train_step(self.handle, batch, int(use_graph), _stream()))
+        N.check(self.lib.b200_engine_train_step(self.handle, batch, int(use_graph), self._s()))
         self.steps += 1
         return self.steps - 1
 
@@ -148,13 +162,13 @@ class NativeEngine:
         """Public streaming API: the batch is copied from (pinned) host memory every step."""
         b = int(images_u8.shape[0])
         N.check(self.lib.b200_engine_train_step_host(self.handle, images_u8.data_ptr(), labels_u8.data_ptr(), b,
-                                                     int(use_graph), _stream()))
+                                                     int(use_graph), self._s()))
         self.steps += 1
         return self.steps - 1
 
     def read_loss(self, step: int) -> float:
         out = ctypes.c_float()
-        N.check(self.lib.b200_engine_read_loss(self.handle, step, ctypes.byref(out), _stream()))
+        N.check(self.lib.b200_engine_read_loss(self.handle, step, ctypes.byref(out), self._s()))
         return float(out.value)
 
     def launches_per_step(self, batch: int) -> int:
@@ -164,7 +178,7 @@ class NativeEngine:
 
     # ---- evaluation
     def evaluate(self, split: int, n: int, batch: int) -> Tuple[float, int]:
-        s = _stream()
+        s = self._s()
         N.check(self.lib.b200_engine_eval_reset(self.handle, s))
         for first in range(0, n, batch):
             N.check(self.lib.b200_engine_eval_batch(self.handle, split, first, min(batch, n - first), s))
@@ -174,8 +188,11 @@ class NativeEngine:
 
     def forward_logp(self, split: int, first: int, batch: int) -> torch.Tensor:
         """Eval-mode log-probabilities of `batch` samples of a split (for tests / inference)."""
-        N.check(self.lib.b200_engine_eval_batch(self.handle, split, first, batch, _stream()))
-        return self.buffer(BUF_LOGP, torch.float32)[: batch * 10].view(batch, 10).clone()
+        N.check(self.lib.b200_engine_eval_batch(self.handle, split, first, batch, self._s()))
+        with self.on_stream():
+            out = self.buffer(BUF_LOGP, torch.float32)[: batch * 10].view(batch, 10).clone()
+        self.synchronize()
+        return out
 
 
 class B200Backend:
@@ -206,6 +223,7 @@ class B200Backend:
         self.engine.set_lr(lr)
         self._pinned_loss = torch.empty(64, dtype=torch.float32).pin_memory()
         self._slot = 0
+        self._epoch_n = len(train)
 
     def begin_epoch(self, indices: torch.Tensor) -> None:
         self._epoch_n = int(indices.numel())
@@ -218,10 +236,11 @@ class B200Backend:
             return None
         slot = self._slot
         self._slot = (self._slot + 1) % 64
-        self._pinned_loss[slot: slot + 1].copy_(self.engine.loss_ring[s % LOSS_RING: s % LOSS_RING + 1],
-                                                non_blocking=True)
-        ev = torch.cuda.Event()
-        ev.record()
+        with self.engine.on_stream():
+            self._pinned_loss[slot: slot + 1].copy_(self.engine.loss_ring[s % LOSS_RING: s % LOSS_RING + 1],
+                                                    non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record()
         return (slot, ev)
 
     def loss(self, token) -> float:
@@ -243,4 +262,4 @@ class B200Backend:
         self.engine.set_state_dict(state)
 
     def finish(self) -> None:
-        torch.cuda.synchronize()
+        self.engine.synchronize()
