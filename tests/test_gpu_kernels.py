@@ -128,6 +128,8 @@ LAYOUTS = [(False, False), (False, True), (True, True), (True, False)]
 def test_gemm(ops, a_mn, b_mn, shape, tc):
     _need_tc(tc)
     M, N, K, splits = shape
+    if tc and ((a_mn and M % 32) or (b_mn and N % 32)):
+        pytest.skip("MN-major tensor-core operands need the MN extent to be a multiple of 32")
     A = torch.randn(M, K, device="cuda")
     B = torch.randn(N, K, device="cuda")
     Aarg = A.t().contiguous() if a_mn else A
