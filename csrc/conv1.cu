@@ -113,24 +113,28 @@ conv1_wgrad_kernel(const uint8_t* __restrict__ images, const int32_t* __restrict
 }
 
 // dst[e] = sum_{p < nparts} src[p*stride + e]  — fixed order, so results are run-to-run identical.
-__global__ void reduce_partials_kernel(float* __restrict__ dst, const float* __restrict__ src, int n,
-                                       int nparts, int stride) {
-  const int e = blockIdx.x * blockDim.x + threadIdx.x;
-  if (e >= n) return;
-  float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
-  int p = 0;
-  for (; p + 4 <= nparts; p += 4) {
-    s0 += src[(size_t)(p + 0) * stride + e];
-    s1 += src[(size_t)(p + 1) * stride + e];
-    s2 += src[(size_t)(p + 2) * stride + e];
-    s3 += src[(size_t)(p + 3) * stride + e];
+// block = 64 outputs x 16 part-slices: slice g sums parts g, g+16, ... serially, slices are combined
+// in a fixed order through shared memory.
+__global__ void __launch_bounds__(1024)
+reduce_partials_kernel(float* __restrict__ dst, const float* __restrict__ src, int n, int nparts, int stride) {
+  __shared__ float red[16][64];
+  const int j = threadIdx.x & 63, g = threadIdx.x >> 6;
+  const int e = blockIdx.x * 64 + j;
+  float s = 0.f;
+  if (e < n)
+    for (int p = g; p < nparts; p += 16) s += src[(size_t)p * stride + e];
+  red[g][j] = s;
+  __syncthreads();
+  if (g == 0 && e < n) {
+    float t = 0.f;
+#pragma unroll
+    for (int q = 0; q < 16; ++q) t += red[q][j];
+    dst[e] = t;
   }
-  for (; p < nparts; ++p) s0 += src[(size_t)p * stride + e];
-  dst[e] = (s0 + s1) + (s2 + s3);
 }
 
 void b200_launch_reduce_partials(float* dst, const float* src, int n, int nparts, int stride, cudaStream_t s) {
-  reduce_partials_kernel<<<ceil_div(n, 128), 128, 0, s>>>(dst, src, n, nparts, stride);
+  reduce_partials_kernel<<<ceil_div(n, 64), 1024, 0, s>>>(dst, src, n, nparts, stride);
   b200_count_launch();
 }
 

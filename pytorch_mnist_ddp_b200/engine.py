@@ -31,7 +31,7 @@ from .utils.data import MnistSplit
 LOSS_RING = 1024
 TC_CONV2_FWD, TC_FC1_FWD, TC_FC1_BWD, TC_CONV2_BWD = 1, 2, 4, 8
 TC_ALL = 15
-DEFAULT_TC = 0
+DEFAULT_TC = TC_ALL
 
 
 def default_tc_mask() -> int:
