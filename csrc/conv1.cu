@@ -66,8 +66,8 @@ conv1_fwd_kernel(const uint8_t* __restrict__ images, const int32_t* __restrict__
   }
 }
 
-// grid = batch, block = 256 (8 pixel groups x 32 channels).  Writes one partial row per image:
-// part[b][0..287] = dW[tap][o], part[b][288..319] = db[o].  A fixed-order reduction follows.
+// grid = 2*batch, block = 256 (8 pixel groups x 32 channels).  Writes one partial row per block:
+// part[blk][0..287] = dW[tap][o], part[blk][288..319] = db[o].  A fixed-order reduction follows.
 constexpr int CONV1_PART = 320;
 __global__ void __launch_bounds__(256)
 conv1_wgrad_kernel(const uint8_t* __restrict__ images, const int32_t* __restrict__ idx,
@@ -75,7 +75,8 @@ conv1_wgrad_kernel(const uint8_t* __restrict__ images, const int32_t* __restrict
                    float* __restrict__ part) {
   __shared__ float x[IMG * IMG];
   __shared__ float red[8][10][C1];
-  const int b = blockIdx.x;
+  // two blocks per image (13 output rows each) so that 2*batch blocks keep every SM busy
+  const int b = blockIdx.x >> 1, half = blockIdx.x & 1;
   const int sample = sample_of(idx, ctrl, b);
   const uint8_t* src = images + (size_t)sample * (IMG * IMG);
   if (threadIdx.x < IMG * IMG / 4) {
@@ -91,14 +92,22 @@ conv1_wgrad_kernel(const uint8_t* __restrict__ images, const int32_t* __restrict
   float acc[10];
 #pragma unroll
   for (int t = 0; t < 10; ++t) acc[t] = 0.f;
-  for (int p = g; p < H1 * W1; p += 8) {
-    const int y = p / W1, xx = p - y * W1;
-    const float d = in[p * C1 + o];
+  constexpr int HALF = (H1 / 2) * W1;  // 338 pixels
+  const int p0 = half * HALF;
+  for (int pb = g; pb < HALF; pb += 32) {
+    float d[4];
 #pragma unroll
-    for (int kh = 0; kh < 3; ++kh)
+    for (int u = 0; u < 4; ++u) d[u] = (pb + 8 * u < HALF) ? in[(p0 + pb + 8 * u) * C1 + o] : 0.f;  // 4 loads in flight
 #pragma unroll
-      for (int kw = 0; kw < 3; ++kw) acc[kh * 3 + kw] = fmaf(d, x[(y + kh) * IMG + xx + kw], acc[kh * 3 + kw]);
-    acc[9] += d;
+    for (int u = 0; u < 4; ++u) {
+      const int p = min(p0 + pb + 8 * u, H1 * W1 - 1);
+      const int y = p / W1, xx = p - y * W1;
+#pragma unroll
+      for (int kh = 0; kh < 3; ++kh)
+#pragma unroll
+        for (int kw = 0; kw < 3; ++kw) acc[kh * 3 + kw] = fmaf(d[u], x[(y + kh) * IMG + xx + kw], acc[kh * 3 + kw]);
+      acc[9] += d[u];
+    }
   }
 #pragma unroll
   for (int t = 0; t < 10; ++t) red[g][t][o] = acc[t];
@@ -108,7 +117,7 @@ conv1_wgrad_kernel(const uint8_t* __restrict__ images, const int32_t* __restrict
     float s = 0.f;
 #pragma unroll
     for (int gg = 0; gg < 8; ++gg) s += red[gg][t][oo];
-    part[(size_t)b * CONV1_PART + e] = s;  // e = t*32+o: taps first (288), then bias (32)
+    part[(size_t)blockIdx.x * CONV1_PART + e] = s;  // e = t*32+o: taps first (288), then bias (32)
   }
 }
 
@@ -151,10 +160,10 @@ extern "C" int b200_conv1_wgrad(const uint8_t* images, const int32_t* idx, const
                                 float* part, float* dw, float* db, int batch, void* stream) {
   B200_REQUIRE(batch > 0, "conv1_wgrad: batch must be > 0");
   cudaStream_t s = (cudaStream_t)stream;
-  conv1_wgrad_kernel<<<batch, 256, 0, s>>>(images, idx, (const B200Ctrl*)ctrl, da1, part);
+  conv1_wgrad_kernel<<<2 * batch, 256, 0, s>>>(images, idx, (const B200Ctrl*)ctrl, da1, part);
   b200_count_launch();
-  b200_launch_reduce_partials(dw, part, 288, batch, CONV1_PART, s);
-  b200_launch_reduce_partials(db, part + 288, 32, batch, CONV1_PART, s);
+  b200_launch_reduce_partials(dw, part, 288, 2 * batch, CONV1_PART, s);
+  b200_launch_reduce_partials(db, part + 288, 32, 2 * batch, CONV1_PART, s);
   B200_LAUNCH_CHECK();
   return B200_OK;
 }

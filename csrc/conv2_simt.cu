@@ -222,21 +222,41 @@ conv2_wgrad_simt_kernel(const float* __restrict__ dp, const uint8_t* __restrict_
   if (ig == 0) dst[W2_ELEMS + o] = accb;
 }
 
-// materialise dY [B][24][24][64] for the TMA-fed tensor-core backward kernels
-__global__ void unpool_dense_kernel(const float* __restrict__ dp, const uint8_t* __restrict__ amax,
-                                    float* __restrict__ dy, int batch) {
+// materialise dY [B][24][24][64] for the TMA-fed tensor-core backward kernels.  Optionally also
+// produces per-block partial sums of dp per channel (= conv2's bias gradient: every non-zero of dY
+// is an element of dp) in db_part[block][64].
+__global__ void __launch_bounds__(256)
+unpool_dense_kernel(const float* __restrict__ dp, const uint8_t* __restrict__ amax, float* __restrict__ dy, int batch,
+                    float* __restrict__ db_part) {
+  __shared__ float4 red[256];
   const size_t n4 = (size_t)batch * HP * WP * (C2 / 4);
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  // gridDim.x * 256 is a multiple of 16, so a thread always sees the same channel quad
   for (size_t e4 = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e4 < n4; e4 += (size_t)gridDim.x * blockDim.x) {
     const int oq = (int)(e4 % (C2 / 4));
     const size_t win = e4 / (C2 / 4);
     const int pw = (int)(win % WP), ph = (int)((win / WP) % HP), b = (int)(win / (WP * HP));
     const float4 d = reinterpret_cast<const float4*>(dp)[e4];
     const uchar4 a = reinterpret_cast<const uchar4*>(amax)[e4];
+    acc.x += d.x; acc.y += d.y; acc.z += d.z; acc.w += d.w;
 #pragma unroll
     for (int s = 0; s < 4; ++s) {
       float4 v = make_float4(a.x == s ? d.x : 0.f, a.y == s ? d.y : 0.f, a.z == s ? d.z : 0.f, a.w == s ? d.w : 0.f);
       const int y = 2 * ph + (s >> 1), x = 2 * pw + (s & 1);
       reinterpret_cast<float4*>(dy)[(((size_t)b * H2 + y) * W2 + x) * (C2 / 4) + oq] = v;
+    }
+  }
+  if (db_part) {
+    red[threadIdx.x] = acc;
+    __syncthreads();
+    if (threadIdx.x < 16) {
+      float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int k = 0; k < 16; ++k) {
+        const float4 r = red[threadIdx.x + 16 * k];
+        t.x += r.x; t.y += r.y; t.z += r.z; t.w += r.w;
+      }
+      reinterpret_cast<float4*>(db_part + (size_t)blockIdx.x * C2)[threadIdx.x] = t;
     }
   }
 }
@@ -290,11 +310,17 @@ extern "C" int b200_conv2_wgrad_simt(const float* dp, const uint8_t* amax, const
   return B200_OK;
 }
 
-extern "C" int b200_unpool_dense(const float* dp, const uint8_t* amax, float* dy, int batch, void* stream) {
+// db_part: scratch of b200_unpool_parts() * 64 floats and db [64], or both NULL to skip the bias gradient
+extern "C" int b200_unpool_parts(void) { return 2 * sm_count(); }
+extern "C" int b200_unpool_dense(const float* dp, const uint8_t* amax, float* dy, float* db_part, float* db, int batch,
+                                 void* stream) {
+  B200_REQUIRE((db_part == nullptr) == (db == nullptr), "unpool_dense: db_part and db go together");
   const size_t n4 = (size_t)batch * HP * WP * (C2 / 4);
-  const int grid = (int)min((size_t)(8 * sm_count()), (n4 + 255) / 256);
-  unpool_dense_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(dp, amax, dy, batch);
+  const int grid = (int)min((size_t)(2 * sm_count()), (n4 + 255) / 256);
+  cudaStream_t s = (cudaStream_t)stream;
+  unpool_dense_kernel<<<grid, 256, 0, s>>>(dp, amax, dy, batch, db_part);
   b200_count_launch();
+  if (db) b200_launch_reduce_partials(db, db_part, C2, grid, C2, s);
   B200_LAUNCH_CHECK();
   return B200_OK;
 }

@@ -101,8 +101,8 @@ int enqueue_train(Engine* E, const uint8_t* images, const uint8_t* labels, const
   // bucket 0 (fc1.*, fc2.*) is complete here
   if (E->hooks.bucket_ready) TRY(E->hooks.bucket_ready(E, 0, s));
   if (E->use_tc & B200_TC_CONV2_BWD) {
-    TRY(b200_unpool_dense(E->dp, E->amax, E->dy, batch, s));
-    TRY(b200_conv2_wgrad_tc(E->dy, E->a1, E->c2_part, G + c.offsets[2], G + c.offsets[3], batch, s));
+    TRY(b200_unpool_dense(E->dp, E->amax, E->dy, E->db_part, G + c.offsets[3], batch, s));
+    TRY(b200_conv2_wgrad_tc(E->dy, E->a1, E->c2_part, G + c.offsets[2], batch, s));
     TRY(b200_conv2_dgrad_tc(E->dy, P + c.offsets[2], E->a1, E->da1, batch, s));
   } else {
     TRY(b200_conv2_wgrad_simt(E->dp, E->amax, E->a1, E->c2_part, G + c.offsets[2], G + c.offsets[3], batch, s));
@@ -205,9 +205,10 @@ extern "C" int b200_engine_create(const B200EngineConfig* cfg, void** out) {
   size_t part_cap = 0;
   for (int b = 1; b <= cfg->max_batch; ++b) part_cap = max(part_cap, (size_t)fc1_splits(b) * b * FC1_OUT);
   A(E->fc1_part, part_cap);
-  A(E->c1_part, B * 320);
+  A(E->c1_part, 2 * B * 320);
   A(E->c2_part, (size_t)E->nsm * (9 * C2 * C1 + C2));
   if (cfg->use_tc & B200_TC_CONV2_BWD) A(E->dy, B * H2 * W2 * C2);
+  A(E->db_part, (size_t)b200_unpool_parts() * C2);
   A(E->loss_ring, (size_t)B200_LOSS_RING);
   A(E->loss_scalar, 4);
   A(E->ctrl, 1);

@@ -31,7 +31,7 @@ struct Engine {
   uint8_t *stage_img = nullptr, *stage_lbl = nullptr;
   float *a1 = nullptr, *da1 = nullptr, *pooled = nullptr, *dp = nullptr, *h = nullptr, *dh = nullptr,
         *dlogits = nullptr, *loss_i = nullptr, *logp = nullptr, *fc1_part = nullptr, *c1_part = nullptr,
-        *c2_part = nullptr, *dy = nullptr, *loss_ring = nullptr, *loss_scalar = nullptr;
+        *c2_part = nullptr, *dy = nullptr, *db_part = nullptr, *loss_ring = nullptr, *loss_scalar = nullptr;
   uint8_t* amax = nullptr;
   int* correct_i = nullptr;
   B200Ctrl *ctrl = nullptr, *ctrl_eval = nullptr;

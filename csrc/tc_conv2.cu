@@ -406,18 +406,6 @@ conv2_wgrad_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_co
   if (warp == 1) tmem_dealloc(tmem_base, 256);
 }
 
-// column sums of dp [B*144][64] -> db partials (the bias gradient; one non-zero per pooling window)
-__global__ void __launch_bounds__(256)
-colsum64_kernel(const float* __restrict__ dp, int rows, float* __restrict__ part) {
-  __shared__ float red[4][C2];
-  const int o = threadIdx.x & 63, g = threadIdx.x >> 6;
-  float s = 0.f;
-  for (int r = blockIdx.x * 4 + g; r < rows; r += gridDim.x * 4) s += dp[(size_t)r * C2 + o];
-  red[g][o] = s;
-  __syncthreads();
-  if (g == 0) part[blockIdx.x * C2 + o] = (red[0][o] + red[1][o]) + (red[2][o] + red[3][o]);
-}
-
 // ---- host ---------------------------------------------------------------------------------------
 struct Key {
   const void* p; int batch, kind;
@@ -501,8 +489,8 @@ extern "C" int b200_conv2_dgrad_tc(const float* dy, const float* w, const float*
   return B200_OK;
 }
 
-extern "C" int b200_conv2_wgrad_tc(const float* dy, const float* a1, float* part, float* dw, float* db, int batch,
-                                   void* stream) {
+// the bias gradient comes from b200_unpool_dense (column sums of the pooled gradient)
+extern "C" int b200_conv2_wgrad_tc(const float* dy, const float* a1, float* part, float* dw, int batch, void* stream) {
   B200_REQUIRE(batch > 0, "conv2_wgrad_tc: batch must be > 0");
   cudaStream_t s = (cudaStream_t)stream;
   CUtensorMap ma, md;
@@ -518,12 +506,6 @@ extern "C" int b200_conv2_wgrad_tc(const float* dy, const float* a1, float* part
   conv2_wgrad_tc_kernel<<<grid, 192, G_SMEM, s>>>(ma, md, part, nkblk);
   b200_count_launch();
   b200_launch_reduce_partials(dw, part, W2_ELEMS, grid, CONV2_PART, s);
-  // bias gradient: every element of dY is an element of the pooled gradient, so sum over all of dY
-  const int rows = batch * H2 * W2;
-  const int cgrid = min(ceil_div(rows, 64), b200_sm_count());
-  colsum64_kernel<<<cgrid, 256, 0, s>>>(dy, rows, part + W2_ELEMS);  // reuses the bias slots: stride 64
-  b200_count_launch();
-  b200_launch_reduce_partials(db, part + W2_ELEMS, C2, cgrid, C2, s);
   B200_LAUNCH_CHECK();
   return B200_OK;
 }

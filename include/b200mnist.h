@@ -35,7 +35,7 @@ int b200_ctrl_bytes(void);
 /* a1[b] = relu(conv1(normalize(images[idx ? idx[pos+b] : pos+b]))), NHWC [B][26][26][32] */
 int b200_conv1_fwd(const uint8_t* images, const int32_t* idx, const void* ctrl, const float* w, const float* bias,
                    float* a1, int batch, void* stream);
-/* part: scratch [batch][320]; dw [9][32]; db [32] */
+/* part: scratch [2*batch][320]; dw [9][32]; db [32] */
 int b200_conv1_wgrad(const uint8_t* images, const int32_t* idx, const void* ctrl, const float* da1, float* part,
                      float* dw, float* db, int batch, void* stream);
 int b200_reduce_partials(float* dst, const float* src, int n, int nparts, int stride, void* stream);
@@ -48,7 +48,11 @@ int b200_conv2_dgrad_simt(const float* dp, const uint8_t* amax, const float* w, 
 int b200_conv2_wgrad_parts(void); /* number of partial slots the wgrad kernels need (18496 floats each) */
 int b200_conv2_wgrad_simt(const float* dp, const uint8_t* amax, const float* a1, float* part, float* dw, float* db,
                           int batch, void* stream);
-int b200_unpool_dense(const float* dp, const uint8_t* amax, float* dy, int batch, void* stream);
+/* dY[B][24][24][64] from the pooled gradient + argmax; optionally conv2's bias gradient db[64]
+ * (db_part: scratch of b200_unpool_parts()*64 floats; pass both or neither) */
+int b200_unpool_parts(void);
+int b200_unpool_dense(const float* dp, const uint8_t* amax, float* dy, float* db_part, float* db, int batch,
+                      void* stream);
 
 /* ---- fp32 SIMT GEMM (mnist_ddp.py:57; SURVEY N6,N11) ------------------------------------------- */
 int b200_sgemm(const float* A, long sam, long sak, const float* B, long sbk, long sbn, float* C, int M, int N, int K,
@@ -67,8 +71,8 @@ int b200_conv2_fwd_tc(const float* a1, const float* w, const float* bias, const 
                       uint8_t* amax, int batch, void* stream);
 /* implicit-GEMM dgrad from the dense dY [B][24][24][64]; epilogue applies conv1's ReLU mask */
 int b200_conv2_dgrad_tc(const float* dy, const float* w, const float* a1, float* da1, int batch, void* stream);
-/* implicit-GEMM wgrad from the dense dY; part as for _simt */
-int b200_conv2_wgrad_tc(const float* dy, const float* a1, float* part, float* dw, float* db, int batch, void* stream);
+/* implicit-GEMM wgrad from the dense dY; part as for _simt; the bias gradient comes from b200_unpool_dense */
+int b200_conv2_wgrad_tc(const float* dy, const float* a1, float* part, float* dw, int batch, void* stream);
 
 /* ---- classifier head (mnist_ddp.py:57-61,71,97-99; SURVEY N7-N10,N22) -------------------------- */
 int b200_head_fused(const float* part, int splits, int batch, const float* b1, const float* w2, const float* b2,

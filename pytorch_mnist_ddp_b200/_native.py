@@ -115,12 +115,12 @@ _SIGNATURES = {
     "b200_conv2_fwd_simt": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _vp],
     "b200_conv2_dgrad_simt": [_vp, _vp, _vp, _vp, _vp, _i, _vp],
     "b200_conv2_wgrad_simt": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _vp],
-    "b200_unpool_dense": [_vp, _vp, _vp, _i, _vp],
+    "b200_unpool_dense": [_vp, _vp, _vp, _vp, _vp, _i, _vp],
     "b200_sgemm": [_vp, _l, _l, _vp, _l, _l, _vp, _i, _i, _i, _i, _i, _vp, _f, _vp],
     "b200_tc_gemm": [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp, _f, _vp],
     "b200_conv2_fwd_tc": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _vp],
     "b200_conv2_dgrad_tc": [_vp, _vp, _vp, _vp, _i, _vp],
-    "b200_conv2_wgrad_tc": [_vp, _vp, _vp, _vp, _vp, _i, _vp],
+    "b200_conv2_wgrad_tc": [_vp, _vp, _vp, _vp, _i, _vp],
     "b200_head_fused": [_vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp],
     "b200_head_wgrad": [_vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp],
     "b200_eval_accumulate": [_vp, _vp, _i, _vp, _vp],

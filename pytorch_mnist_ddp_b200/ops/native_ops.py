@@ -51,7 +51,7 @@ def conv1_fwd(images_u8: torch.Tensor, idx: Optional[torch.Tensor], ctrl: torch.
 
 def conv1_wgrad(images_u8, idx, ctrl, da1: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
     batch = da1.shape[0]
-    part = torch.empty(batch, 320, device="cuda")
+    part = torch.empty(2 * batch, 320, device="cuda")
     dw, db = torch.empty(9, 32, device="cuda"), torch.empty(32, device="cuda")
     N.check(N.lib().b200_conv1_wgrad(_p(images_u8), _p(idx), _p(ctrl), _p(da1), _p(part), _p(dw), _p(db), batch, _s()))
     return dw, db
@@ -66,11 +66,17 @@ def conv2_fwd(a1: torch.Tensor, w: torch.Tensor, b: torch.Tensor, ctrl: torch.Te
     return pooled, amax
 
 
-def unpool_dense(dp: torch.Tensor, amax: torch.Tensor) -> torch.Tensor:
+def unpool_dense(dp: torch.Tensor, amax: torch.Tensor, with_db: bool = False):
     batch = dp.shape[0]
+    L = N.lib()
     dy = torch.empty(batch, 24, 24, 64, device="cuda")
-    N.check(N.lib().b200_unpool_dense(_p(dp), _p(amax), _p(dy), batch, _s()))
-    return dy
+    if not with_db:
+        N.check(L.b200_unpool_dense(_p(dp), _p(amax), _p(dy), None, None, batch, _s()))
+        return dy
+    part = torch.empty(L.b200_unpool_parts() * 64, device="cuda")
+    db = torch.empty(64, device="cuda")
+    N.check(L.b200_unpool_dense(_p(dp), _p(amax), _p(dy), _p(part), _p(db), batch, _s()))
+    return dy, db
 
 
 def conv2_dgrad(dp, amax, w, a1, tc: bool = False) -> torch.Tensor:
@@ -90,8 +96,8 @@ def conv2_wgrad(dp, amax, a1, tc: bool = False) -> Tuple[torch.Tensor, torch.Ten
     part = torch.empty(L.b200_conv2_wgrad_parts() * (18432 + 64), device="cuda")
     dw, db = torch.empty(9, 64, 32, device="cuda"), torch.empty(64, device="cuda")
     if tc:
-        dy = unpool_dense(dp, amax)
-        N.check(L.b200_conv2_wgrad_tc(_p(dy), _p(a1), _p(part), _p(dw), _p(db), batch, _s()))
+        dy, db = unpool_dense(dp, amax, with_db=True)
+        N.check(L.b200_conv2_wgrad_tc(_p(dy), _p(a1), _p(part), _p(dw), batch, _s()))
     else:
         N.check(L.b200_conv2_wgrad_simt(_p(dp), _p(amax), _p(a1), _p(part), _p(dw), _p(db), batch, _s()))
     return dw, db
