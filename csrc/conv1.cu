@@ -7,6 +7,8 @@
 //             Replaces the reference's DataLoader worker, H2D copy, cuDNN conv, bias add and ReLU
 //             kernels.
 //   wgrad   : dW[tap][o] = sum da1 * x, db[o] = sum da1; input needs no gradient.
+#include <mutex>
+
 #include "common.cuh"
 
 using namespace net;
@@ -170,6 +172,73 @@ extern "C" int b200_conv1_wgrad(const uint8_t* images, const int32_t* idx, const
 
 extern "C" int b200_reduce_partials(float* dst, const float* src, int n, int nparts, int stride, void* stream) {
   b200_launch_reduce_partials(dst, src, n, nparts, stride, (cudaStream_t)stream);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// conv1 weight gradient for callers that must not allocate device memory.
+//
+// b200_conv1_wgrad needs a scratch buffer of 2*batch*320 floats for its per-block partial sums,
+// and somebody has to allocate it.  Some users of this library cannot: a host process whose GPU
+// memory has been handed over in full to another allocator (a framework memory pool sized to the
+// whole device leaves nothing for a stray cudaMalloc), or a control loop with a latency budget
+// that cudaMalloc/cudaFree would break because both synchronise the whole device.  For them the
+// scratch lives in the library image itself: a file-scope device array that every GPU loading
+// this library carries until the process exits (B200_NOALLOC_MAX_BATCH * 2 * 320 floats
+// = 2.5 MiB), so the entry point below never calls cudaMalloc, cudaFree, or any routine that
+// allocates.
+//
+// Things a caller has to know:
+//  * batch may not exceed B200_NOALLOC_MAX_BATCH (1024); larger batches are refused with
+//    B200_ERR_ARG and a message, nothing is launched.
+//  * Inside host code the name `g_noalloc_scratch` is only a handle for the symbol, not a device
+//    address; the real address is looked up with cudaGetSymbolAddress the first time the entry
+//    point runs on a given device (with that device current) and remembered per device.  That
+//    first call per device does the look-up, so make it before starting any stream capture.
+//  * All calls on one device share the one array, and it keeps whatever the previous call left
+//    in it.  Nothing in it has to start at zero: a call overwrites every partial row it later
+//    reads (rows 0 .. 2*batch-1) before the reduction kernels read them.  Two calls whose kernels
+//    can overlap on the GPU (different streams without ordering between them) would write the
+//    same rows at the same time and corrupt each other: keep calls on one device ordered.
+// ---------------------------------------------------------------------------------------------
+#define B200_NOALLOC_MAX_BATCH 1024
+static __device__ __align__(256) float g_noalloc_scratch[(size_t)B200_NOALLOC_MAX_BATCH * 2 * CONV1_PART];
+
+static int noalloc_scratch_for_current_device(float** out) {
+  constexpr int MAX_DEVICES = 64;
+  static float* cached[MAX_DEVICES] = {nullptr};
+  static std::mutex mu;
+  int dev = -1;
+  B200_CHECK(cudaGetDevice(&dev));
+  B200_REQUIRE(dev >= 0 && dev < MAX_DEVICES, "conv1_wgrad_noalloc: device ordinal %d not supported", dev);
+  std::lock_guard<std::mutex> lk(mu);
+  if (!cached[dev]) {
+    float* p = nullptr;
+    B200_CHECK(cudaGetSymbolAddress((void**)&p, g_noalloc_scratch));  // device `dev` is current here
+    B200_REQUIRE(p != nullptr, "conv1_wgrad_noalloc: symbol look-up returned a null address on device %d", dev);
+    cached[dev] = p;
+  }
+  *out = cached[dev];
+  return B200_OK;
+}
+
+extern "C" int b200_conv1_wgrad_noalloc_max_batch(void) { return B200_NOALLOC_MAX_BATCH; }
+
+extern "C" int b200_conv1_wgrad_noalloc(const uint8_t* images, const int32_t* idx, const void* ctrl, const float* da1,
+                                        float* dw, float* db, int batch, void* stream) {
+  B200_REQUIRE(batch > 0, "conv1_wgrad_noalloc: batch must be > 0");
+  B200_REQUIRE(batch <= B200_NOALLOC_MAX_BATCH,
+               "conv1_wgrad_noalloc: batch %d exceeds the built-in scratch (max %d samples); use b200_conv1_wgrad "
+               "with a caller-provided scratch buffer instead", batch, B200_NOALLOC_MAX_BATCH);
+  float* scratch = nullptr;
+  int r = noalloc_scratch_for_current_device(&scratch);
+  if (r != B200_OK) return r;
+  cudaStream_t s = (cudaStream_t)stream;
+  conv1_wgrad_kernel<<<2 * batch, 256, 0, s>>>(images, idx, (const B200Ctrl*)ctrl, da1, scratch);
+  b200_count_launch();
+  b200_launch_reduce_partials(dw, scratch, 288, 2 * batch, CONV1_PART, s);
+  b200_launch_reduce_partials(db, scratch + 288, 32, 2 * batch, CONV1_PART, s);
   B200_LAUNCH_CHECK();
   return B200_OK;
 }

@@ -39,6 +39,18 @@ int b200_conv1_fwd(const uint8_t* images, const int32_t* idx, const void* ctrl, 
 int b200_conv1_wgrad(const uint8_t* images, const int32_t* idx, const void* ctrl, const float* da1, float* part,
                      float* dw, float* db, int batch, void* stream);
 int b200_reduce_partials(float* dst, const float* src, int n, int nparts, int stride, void* stream);
+/* Same result as b200_conv1_wgrad, for callers that cannot allocate device memory (their GPU memory
+ * belongs to another allocator, or a cudaMalloc's device-wide synchronisation is unaffordable).  This
+ * entry point has no counterpart in the reference.  The partial-sum scratch is a 2.5 MiB array built
+ * into the library image (held by every GPU that loads the library until the process exits), so no
+ * cudaMalloc/cudaFree or allocating routine is called.  batch <= b200_conv1_wgrad_noalloc_max_batch()
+ * (1024); larger batches fail with B200_ERR_ARG.  The first call on each device looks the array's
+ * address up (cudaGetSymbolAddress, that device current): make that call before any stream capture.
+ * All calls on a device share the array and it keeps the last call's contents (nothing needs
+ * clearing: every row that is read is rewritten first); calls that can overlap on the GPU race. */
+int b200_conv1_wgrad_noalloc_max_batch(void);
+int b200_conv1_wgrad_noalloc(const uint8_t* images, const int32_t* idx, const void* ctrl, const float* da1, float* dw,
+                             float* db, int batch, void* stream);
 
 /* ---- conv2 on CUDA cores (mnist_ddp.py:52-55; SURVEY N2-N5,N12,N13) ---------------------------- */
 int b200_conv2_fwd_simt(const float* a1, const float* w, const float* bias, const void* ctrl, float* pooled,

@@ -112,6 +112,7 @@ _SIGNATURES = {
     "b200_conv1_fwd": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _vp],
     "b200_conv1_wgrad": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp],
     "b200_reduce_partials": [_vp, _vp, _i, _i, _i, _vp],
+    "b200_conv1_wgrad_noalloc": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _vp],
     "b200_conv2_fwd_simt": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _vp],
     "b200_conv2_dgrad_simt": [_vp, _vp, _vp, _vp, _vp, _i, _vp],
     "b200_conv2_wgrad_simt": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _vp],
