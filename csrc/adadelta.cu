@@ -12,13 +12,6 @@
 // makes this kernel the "end of step" marker inside the replayed CUDA graph.
 #include "common.cuh"
 
-__device__ __forceinline__ void adadelta_update(float g, float& p, float& v, float& u, float lr, float rho, float eps) {
-  v = fmaf(v, rho, (1.f - rho) * g * g);
-  const float d = __fdiv_rn(sqrtf(u + eps), sqrtf(v + eps)) * g;
-  u = fmaf(u, rho, (1.f - rho) * d * d);
-  p = fmaf(-lr, d, p);
-}
-
 __global__ void __launch_bounds__(256)
 adadelta_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ v, float* __restrict__ u,
                 int n4, B200Ctrl* __restrict__ ctrl, float rho, float eps, int advance_batch,

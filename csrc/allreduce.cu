@@ -1,0 +1,338 @@
+// Fused gradient all-reduce + 1/world averaging + Adadelta over NVLink peer memory.
+//
+// This is the replacement for DistributedDataParallel's communication path (mnist_ddp.py:173 and
+// what fires inside loss.backward() / optimizer.step(), mnist_ddp.py:72-73; SURVEY N15, N17, C1-C4,
+// K25, section 8 rows 11, 12, 14, 17).  Per gradient bucket the reference runs: 4 bucket-copy kernels
+// with the 1/W scale, one ncclAllReduce, 4 copy-back kernels, and later ~12 multi-tensor optimizer
+// kernels.  Here a bucket is ONE kernel: every CTA joins a cross-GPU barrier, then loads the W ranks'
+// gradient slices straight from their (IPC-mapped) buckets, sums them in a fixed rank order — so all
+// ranks get bit-identical results — scales, applies the Adadelta update and writes parameters.
+//
+//   one-shot : every rank reduces the whole bucket and updates its full replica.  (W-1)*S bytes in per
+//              GPU; best for latency-bound sizes (the 75 KB conv bucket, everything at W = 2).
+//   two-shot : rank r reduces slice r only (reduce-scatter), runs Adadelta on that slice with its own
+//              shard of the optimizer state, and stores the updated PARAMETERS into every peer
+//              (all-gather of parameters, not of gradients).  2*(W-1)/W*S bytes per GPU.
+// Both end with a second barrier: peers may not overwrite their gradient buckets (next backward)
+// until everybody has finished reading them, and in two-shot nobody may start the next forward until
+// every slice of the parameters has landed.
+//
+// Barriers are flag words in the symmetric arena: CTA b of rank r writes a monotonically increasing
+// token (derived from the device-side step counter, so the kernel is CUDA-graph replayable) into slot
+// [b][r] of every peer with st.release.sys and spins with ld.acquire.sys on its own slots.  Spins are
+// bounded and trap.  The kernels also run all ranks inside ONE cooperative launch (blockIdx.y = rank)
+// so that they can be tested on a single GPU.
+#include <vector>
+
+#include "common.cuh"
+#include "engine.h"
+#include "symm.h"
+
+namespace {
+
+struct CommArgs {
+  const float* grad[SYMM_MAX_WORLD];  // start of the bucket in every rank's gradient buffer
+  float* param[SYMM_MAX_WORLD];       // start of the bucket in every rank's parameter (or output) buffer
+  uint32_t* flags[SYMM_MAX_WORLD];    // every rank's flag block
+  float* v;                           // local Adadelta state (bucket start); unused when OPT == false
+  float* u;
+  const B200Ctrl* ctrl;               // lr and step counter; may be null when token != 0 and OPT == false
+  int rank, world, n4, channel;
+  float inv_world;
+};
+
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ float4 ld_peer_f4(const float* p) {  // never served from a stale L1 line
+  float4 r;
+  asm volatile("ld.volatile.global.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p) : "memory");
+  return r;
+}
+__device__ __forceinline__ void st_peer_f4(float* p, float4 v) {
+  asm volatile("st.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+
+// phase 0 = "my gradients are complete", phase 1 = "I have finished reading / my writes are out"
+__device__ __forceinline__ void comm_barrier(const CommArgs& a, int phase, uint32_t tok) {
+  __threadfence_system();
+  __syncthreads();
+  if ((int)threadIdx.x < a.world) {
+    const int idx = ((a.channel * 2 + phase) * SYMM_MAX_BLOCKS + blockIdx.x) * SYMM_MAX_WORLD;
+    st_release_sys(a.flags[threadIdx.x] + idx + a.rank, tok);
+    const uint32_t* mine = a.flags[a.rank] + idx + threadIdx.x;
+    uint32_t spins = 0;
+    while ((int32_t)(ld_acquire_sys(mine) - tok) < 0) {
+      if (++spins > (1u << 27)) __trap();  // a peer never arrived: fail loudly instead of hanging
+    }
+  }
+  __syncthreads();
+}
+
+template <int MODE, bool OPT>
+__global__ void __launch_bounds__(512)
+fused_allreduce_kernel(const CommArgs* __restrict__ table, uint32_t token, float rho, float eps) {
+  const CommArgs& a = table[blockIdx.y];
+  const int W = a.world, r = a.rank;
+  const uint32_t tok = token ? token : (uint32_t)(a.ctrl->step) * 2u + 1u;
+  const float lr = OPT ? a.ctrl->lr : 0.f;
+  const float inv_w = a.inv_world;
+  const float* gp[SYMM_MAX_WORLD];
+  float* pp[SYMM_MAX_WORLD];
+#pragma unroll
+  for (int q = 0; q < SYMM_MAX_WORLD; ++q) { gp[q] = a.grad[q < W ? q : 0]; pp[q] = a.param[q < W ? q : 0]; }
+
+  comm_barrier(a, 0, tok);
+
+  int lo = 0, hi = a.n4;
+  if (MODE == 1) {
+    const int per = (a.n4 + W - 1) / W;
+    lo = min(a.n4, r * per);
+    hi = min(a.n4, lo + per);
+  }
+  const int stride = gridDim.x * blockDim.x;
+  for (int i = lo + blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += stride) {
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+    for (int q = 0; q < SYMM_MAX_WORLD; ++q) {
+      if (q < W) {
+        const float4 g = ld_peer_f4(gp[q] + 4 * (size_t)i);
+        s.x += g.x; s.y += g.y; s.z += g.z; s.w += g.w;
+      }
+    }
+    s.x *= inv_w; s.y *= inv_w; s.z *= inv_w; s.w *= inv_w;
+    float4 out = s;
+    if (OPT) {
+      float4 p = *reinterpret_cast<const float4*>(a.param[r] + 4 * (size_t)i);
+      float4 vv = *reinterpret_cast<const float4*>(a.v + 4 * (size_t)i);
+      float4 uu = *reinterpret_cast<const float4*>(a.u + 4 * (size_t)i);
+      adadelta_update(s.x, p.x, vv.x, uu.x, lr, rho, eps);
+      adadelta_update(s.y, p.y, vv.y, uu.y, lr, rho, eps);
+      adadelta_update(s.z, p.z, vv.z, uu.z, lr, rho, eps);
+      adadelta_update(s.w, p.w, vv.w, uu.w, lr, rho, eps);
+      *reinterpret_cast<float4*>(a.v + 4 * (size_t)i) = vv;
+      *reinterpret_cast<float4*>(a.u + 4 * (size_t)i) = uu;
+      out = p;
+    }
+    if (MODE == 0) {
+      *reinterpret_cast<float4*>(a.param[r] + 4 * (size_t)i) = out;
+    } else {
+#pragma unroll
+      for (int q = 0; q < SYMM_MAX_WORLD; ++q)
+        if (q < W) st_peer_f4(pp[q] + 4 * (size_t)i, out);
+    }
+  }
+  comm_barrier(a, 1, tok + 1u);
+}
+
+struct CommPlan {
+  CommArgs* dev = nullptr;  // world_slots entries (1, or W when emulated)
+  int slots = 1;
+  int n4 = 0, world = 1;
+};
+
+int plan_from_arenas(SymmArena* const* arenas, int slots, size_t grad_off, size_t param_off, size_t v_off,
+                     size_t u_off, size_t n_floats, int channel, const B200Ctrl* const* ctrls, CommPlan** out) {
+  B200_REQUIRE(n_floats % 4 == 0 && grad_off % 4 == 0 && param_off % 4 == 0, "comm plan: offsets/size must be x4 floats");
+  B200_REQUIRE(channel >= 0 && channel < SYMM_CHANNELS, "comm plan: channel %d out of range", channel);
+  std::vector<CommArgs> host(slots);
+  for (int sidx = 0; sidx < slots; ++sidx) {
+    SymmArena* a = arenas[sidx];
+    B200_REQUIRE((grad_off + n_floats) * 4 <= a->payload && (param_off + n_floats) * 4 <= a->payload,
+                 "comm plan: bucket exceeds the arena payload");
+    CommArgs& c = host[sidx];
+    memset(&c, 0, sizeof(c));
+    for (int q = 0; q < a->world; ++q) {
+      B200_REQUIRE(a->peer[q], "comm plan: rank %d is not mapped (import the IPC handles first)", q);
+      c.grad[q] = (const float*)a->peer[q] + grad_off;
+      c.param[q] = (float*)a->peer[q] + param_off;
+      c.flags[q] = a->flags(q);
+    }
+    c.v = (float*)a->peer[a->rank] + v_off;
+    c.u = (float*)a->peer[a->rank] + u_off;
+    c.ctrl = ctrls ? ctrls[sidx] : nullptr;
+    c.rank = a->rank;
+    c.world = a->world;
+    c.n4 = (int)(n_floats / 4);
+    c.channel = channel;
+    c.inv_world = 1.0f / (float)a->world;
+  }
+  CommPlan* p = new CommPlan();
+  p->slots = slots;
+  p->n4 = (int)(n_floats / 4);
+  p->world = arenas[0]->world;
+  B200_CHECK(cudaMalloc(&p->dev, sizeof(CommArgs) * slots));
+  B200_CHECK(cudaMemcpy(p->dev, host.data(), sizeof(CommArgs) * slots, cudaMemcpyHostToDevice));
+  *out = p;
+  return B200_OK;
+}
+
+int default_blocks(const CommPlan* p, int mode) {
+  const int work = mode == 1 ? (p->n4 + p->world - 1) / p->world : p->n4;
+  int nb = (work + 1023) / 1024;  // ~2 float4 per thread
+  if (nb < 1) nb = 1;
+  const int cap = p->slots > 1 ? max(1, (b200_sm_count() * 2) / p->slots) : 64;
+  return min(min(nb, cap), SYMM_MAX_BLOCKS);
+}
+
+int run_plan(const CommPlan* p, int mode, int opt, uint32_t token, int nblocks, float rho, float eps, cudaStream_t s) {
+  B200_REQUIRE(p && (mode == 0 || mode == 1), "comm run: bad plan/mode");
+  if (nblocks <= 0) nblocks = default_blocks(p, mode);
+  B200_REQUIRE(nblocks <= SYMM_MAX_BLOCKS, "comm run: at most %d CTAs", SYMM_MAX_BLOCKS);
+  dim3 grid(nblocks, p->slots);
+  const CommArgs* tab = p->dev;
+  void* args[] = {(void*)&tab, (void*)&token, (void*)&rho, (void*)&eps};
+  const void* fn = mode == 0 ? (opt ? (const void*)fused_allreduce_kernel<0, true> : (const void*)fused_allreduce_kernel<0, false>)
+                             : (opt ? (const void*)fused_allreduce_kernel<1, true> : (const void*)fused_allreduce_kernel<1, false>);
+  if (p->slots > 1) {
+    // emulated ranks wait on each other inside one launch: all CTAs must be co-resident
+    B200_CHECK(cudaLaunchCooperativeKernel(fn, grid, dim3(512), args, 0, s));
+  } else {
+    B200_CHECK(cudaLaunchKernel(fn, grid, dim3(512), args, 0, s));
+  }
+  b200_count_launch();
+  return B200_OK;
+}
+
+// ---- engine hooks ---------------------------------------------------------------------------------
+struct DdpState {
+  CommPlan* plan[2] = {nullptr, nullptr};
+  int mode[2] = {0, 0};
+  cudaStream_t comm = nullptr;
+  cudaEvent_t fork = nullptr, join = nullptr;
+};
+
+__global__ void ctrl_advance_kernel(B200Ctrl* c, int advance) {
+  c->step += 1;
+  c->pos += advance;
+}
+
+int hook_bucket_ready(Engine* E, int bucket, cudaStream_t s) {
+  DdpState* d = (DdpState*)E->hooks.state;
+  if (bucket == 0) {
+    // fc buckets are complete while the conv backward still runs: reduce them on a side stream
+    B200_CHECK(cudaEventRecord(d->fork, s));
+    B200_CHECK(cudaStreamWaitEvent(d->comm, d->fork, 0));
+    int r = run_plan(d->plan[0], d->mode[0], 1, 0, 0, 0.9f, 1e-6f, d->comm);
+    if (r != B200_OK) return r;
+    B200_CHECK(cudaEventRecord(d->join, d->comm));
+    return B200_OK;
+  }
+  return run_plan(d->plan[1], d->mode[1], 1, 0, 0, 0.9f, 1e-6f, s);
+}
+
+int hook_step_end(Engine* E, int advance, cudaStream_t s) {
+  DdpState* d = (DdpState*)E->hooks.state;
+  B200_CHECK(cudaStreamWaitEvent(s, d->join, 0));
+  ctrl_advance_kernel<<<1, 1, 0, s>>>(E->ctrl, advance);
+  b200_count_launch();
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+void hook_destroy(Engine* E) {
+  DdpState* d = (DdpState*)E->hooks.state;
+  if (!d) return;
+  for (int k = 0; k < 2; ++k)
+    if (d->plan[k]) { cudaFree(d->plan[k]->dev); delete d->plan[k]; }
+  if (d->comm) cudaStreamDestroy(d->comm);
+  if (d->fork) cudaEventDestroy(d->fork);
+  if (d->join) cudaEventDestroy(d->join);
+  delete d;
+  E->hooks.state = nullptr;
+}
+
+}  // namespace
+
+// ---- C ABI --------------------------------------------------------------------------------------
+// A plan binds one bucket (offsets in floats inside the arena payload) to a barrier channel.
+extern "C" int b200_comm_plan_create(void* arena, size_t grad_off, size_t param_off, size_t v_off, size_t u_off,
+                                     size_t n_floats, int channel, const void* ctrl, void** plan_out) {
+  B200_REQUIRE(arena && plan_out, "comm_plan_create: null argument");
+  SymmArena* a = (SymmArena*)arena;
+  const B200Ctrl* c = (const B200Ctrl*)ctrl;
+  CommPlan* p = nullptr;
+  int r = plan_from_arenas(&a, 1, grad_off, param_off, v_off, u_off, n_floats, channel, ctrl ? &c : nullptr, &p);
+  if (r != B200_OK) return r;
+  *plan_out = p;
+  return B200_OK;
+}
+
+// all `world` emulated arenas at once; ctrls: world control blocks (or NULL)
+extern "C" int b200_comm_plan_create_emulated(void** arenas, int world, size_t grad_off, size_t param_off, size_t v_off,
+                                              size_t u_off, size_t n_floats, int channel, const void** ctrls,
+                                              void** plan_out) {
+  B200_REQUIRE(arenas && plan_out && world >= 1 && world <= SYMM_MAX_WORLD, "comm_plan_create_emulated: bad arguments");
+  CommPlan* p = nullptr;
+  int r = plan_from_arenas((SymmArena* const*)arenas, world, grad_off, param_off, v_off, u_off, n_floats, channel,
+                           (const B200Ctrl* const*)ctrls, &p);
+  if (r != B200_OK) return r;
+  *plan_out = p;
+  return B200_OK;
+}
+
+extern "C" int b200_comm_plan_destroy(void* plan) {
+  CommPlan* p = (CommPlan*)plan;
+  if (!p) return B200_OK;
+  cudaFree(p->dev);
+  delete p;
+  return B200_OK;
+}
+
+// mode 0 one-shot, 1 two-shot.  opt 1: fused 1/W + Adadelta (needs ctrl in the plan), 0: plain averaged
+// all-reduce into the `param_off` buffer.  token 0: derive the barrier token from ctrl->step; otherwise
+// the caller supplies a token that grows by 2 from call to call.  nblocks 0: pick automatically.
+extern "C" int b200_comm_run(void* plan, int mode, int opt, unsigned int token, int nblocks, void* stream) {
+  return run_plan((const CommPlan*)plan, mode, opt, token, nblocks, 0.9f, 1e-6f, (cudaStream_t)stream);
+}
+
+// Installs the data-parallel hooks on an engine whose params/grads/state live in `arena`
+// (payload layout in floats: [params T][grads T][sq_avg T][acc_delta T]).
+extern "C" int b200_ddp_attach(void* engine, void* arena, int mode_bucket0, int mode_bucket1) {
+  Engine* E = (Engine*)engine;
+  SymmArena* a = (SymmArena*)arena;
+  B200_REQUIRE(E && a, "ddp_attach: null argument");
+  const size_t T = (size_t)E->cfg.param_floats;
+  B200_REQUIRE(a->payload >= 4 * T * 4, "ddp_attach: arena too small for params+grads+state");
+  B200_REQUIRE((float*)a->peer[a->rank] == E->P && E->G[0] == E->P + T && E->V == E->P + 2 * T && E->U == E->P + 3 * T,
+               "ddp_attach: the engine must have been created on this arena's buffers");
+  DdpState* d = new DdpState();
+  d->mode[0] = mode_bucket0;
+  d->mode[1] = mode_bucket1;
+  const B200Ctrl* ctrl = E->ctrl;
+  for (int k = 0; k < 2; ++k) {
+    const size_t beg = (size_t)E->cfg.bucket_begin[k], n = (size_t)(E->cfg.bucket_end[k] - E->cfg.bucket_begin[k]);
+    int r = plan_from_arenas(&a, 1, T + beg, beg, 2 * T + beg, 3 * T + beg, n, k, &ctrl, &d->plan[k]);
+    if (r != B200_OK) return r;
+  }
+  B200_CHECK(cudaStreamCreateWithFlags(&d->comm, cudaStreamNonBlocking));
+  B200_CHECK(cudaEventCreateWithFlags(&d->fork, cudaEventDisableTiming));
+  B200_CHECK(cudaEventCreateWithFlags(&d->join, cudaEventDisableTiming));
+  E->hooks.state = d;
+  E->hooks.bucket_ready = hook_bucket_ready;
+  E->hooks.step_end = hook_step_end;
+  E->hooks.destroy = hook_destroy;
+  return B200_OK;
+}
+
+// copy `n_floats` starting at float offset `off` from rank `src`'s arena into the local one (init only)
+__global__ void peer_copy_kernel(float4* __restrict__ dst, const float4* __restrict__ src, size_t n4) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x)
+    dst[i] = src[i];
+}
+extern "C" int b200_symm_pull(void* arena, int src, size_t off, size_t n_floats, void* stream) {
+  SymmArena* a = (SymmArena*)arena;
+  B200_REQUIRE(a && src >= 0 && src < a->world && off % 4 == 0 && n_floats % 4 == 0, "symm_pull: bad arguments");
+  if (src == a->rank) return B200_OK;
+  peer_copy_kernel<<<64, 512, 0, (cudaStream_t)stream>>>((float4*)((float*)a->peer[a->rank] + off),
+                                                        (const float4*)((const float*)a->peer[src] + off), n_floats / 4);
+  b200_count_launch();
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}

@@ -111,4 +111,13 @@ __device__ __forceinline__ float4 ld_nc_f4(const float* p) {
   return r;
 }
 
+// One Adadelta element update (LIB:torch/optim/adadelta.py:292-302), shared by the single-GPU
+// kernel (adadelta.cu) and the fused all-reduce kernels (allreduce.cu).
+__device__ __forceinline__ void adadelta_update(float g, float& p, float& v, float& u, float lr, float rho, float eps) {
+  v = fmaf(v, rho, (1.f - rho) * g * g);
+  const float d = __fdiv_rn(sqrtf(u + eps), sqrtf(v + eps)) * g;
+  u = fmaf(u, rho, (1.f - rho) * d * d);
+  p = fmaf(-lr, d, p);
+}
+
 static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }

@@ -112,7 +112,7 @@ int enqueue_train(Engine* E, const uint8_t* images, const uint8_t* labels, const
   if (E->hooks.bucket_ready) {
     TRY(E->hooks.bucket_ready(E, 1, s));
     TRY(E->hooks.step_end(E, advance, s));
-  } else {
+  } else if (!E->defer_update) {
     TRY(b200_adadelta(P, G, E->V, E->U, c.param_floats, E->ctrl, 0.9f, 1e-6f, advance, E->done_counter, s));
   }
   return B200_OK;
@@ -131,7 +131,7 @@ std::map<std::pair<Engine*, GraphKey>, GraphVal> g_graphs;
 int run_step(Engine* E, const uint8_t* images, const uint8_t* labels, const int32_t* idx, int batch, int advance,
              int mode, int use_graph, cudaStream_t s) {
   if (!use_graph) return enqueue_train(E, images, labels, idx, batch, advance, s);
-  mode += E->dropout ? 0 : 8;
+  mode += (E->dropout ? 0 : 8) + (E->defer_update ? 16 : 0);
   auto key = std::make_pair(E, GraphKey{batch, mode});
   auto it = g_graphs.find(key);
   if (it == g_graphs.end()) {
@@ -313,6 +313,22 @@ extern "C" int b200_engine_set_dropout(void* engine, int on, void* stream) {
   ctrl_train_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(E->ctrl, on ? 3 : 1);
   B200_LAUNCH_CHECK();
   return B200_OK;
+}
+
+// Baseline ("--comm nccl") support: with defer = 1 a train step stops after backward; the caller
+// reduces the gradient buffer itself (e.g. ncclAllReduce) and then calls b200_engine_apply_update.
+extern "C" int b200_engine_set_defer_update(void* engine, int defer) {
+  Engine* E = (Engine*)engine;
+  B200_REQUIRE(E && !E->hooks.bucket_ready, "engine_set_defer_update: not available with fused data-parallel hooks");
+  E->defer_update = defer != 0;
+  return B200_OK;
+}
+
+extern "C" int b200_engine_apply_update(void* engine, int advance, void* stream) {
+  Engine* E = (Engine*)engine;
+  B200_REQUIRE(E, "engine_apply_update: null engine");
+  return b200_adadelta(E->P, E->G[0], E->V, E->U, E->cfg.param_floats, E->ctrl, 0.9f, 1e-6f, advance, E->done_counter,
+                       stream);
 }
 
 extern "C" int b200_engine_train_step(void* engine, int batch, int use_graph, void* stream) {

@@ -39,6 +39,7 @@ struct Engine {
   double* eval_acc = nullptr;
   void* h_scratch = nullptr;  // 64 B pinned
   unsigned long long steps = 0;
+  bool defer_update = false;  // true: train_step stops after backward (unfused NCCL baseline)
   bool dropout = true;  // false: train without dropout (numerics / DDP-equivalence tests)
   std::set<std::pair<int, int>> warm_batches;  // (batch, mode) pairs that already ran eagerly once
   EngineHooks hooks;

@@ -1,0 +1,21 @@
+// Symmetric-memory arena shared by symm.cu (set-up) and allreduce.cu (kernels, engine hooks).
+#pragma once
+#include <stddef.h>
+#include <stdint.h>
+
+constexpr int SYMM_MAX_WORLD = 8;
+constexpr int SYMM_MAX_BLOCKS = 128;   // CTAs per communication kernel
+constexpr int SYMM_CHANNELS = 4;       // independent barrier channels (bucket 0, bucket 1, microbench, spare)
+// flag word index: ((channel * 2 + phase) * SYMM_MAX_BLOCKS + block) * SYMM_MAX_WORLD + source_rank
+constexpr int SYMM_FLAG_WORDS = SYMM_CHANNELS * 2 * SYMM_MAX_BLOCKS * SYMM_MAX_WORLD;
+constexpr int SYMM_FLAG_BYTES = SYMM_FLAG_WORDS * 4;
+
+struct SymmArena {
+  int world = 1, rank = 0, device = 0;
+  size_t payload = 0;                      // bytes before the flag block
+  void* peer[SYMM_MAX_WORLD] = {nullptr};  // base address of every rank's arena as mapped in THIS process
+  bool opened[SYMM_MAX_WORLD] = {false};
+  bool owns[SYMM_MAX_WORLD] = {false};
+  bool emulated = false;
+  uint32_t* flags(int q) const { return (uint32_t*)((char*)peer[q] + payload); }
+};

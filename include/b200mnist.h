@@ -131,6 +131,10 @@ int b200_engine_begin_epoch(void* engine, const int32_t* idx_host, int n, void* 
 int b200_engine_set_lr(void* engine, float lr, void* stream);
 /* on = 0 trains without dropout (for numerics / data-parallel equivalence tests); default on */
 int b200_engine_set_dropout(void* engine, int on, void* stream);
+/* unfused baseline: with defer = 1 train_step stops after backward; reduce the gradient buffer yourself,
+ * then b200_engine_apply_update runs Adadelta and advances the cursor by `advance` samples */
+int b200_engine_set_defer_update(void* engine, int defer);
+int b200_engine_apply_update(void* engine, int advance, void* stream);
 /* one optimizer step on `batch` samples starting at the cursor: forward, backward, (all-reduce,)
  * Adadelta; replayed from a CUDA graph when use_graph != 0.  Asynchronous. */
 int b200_engine_train_step(void* engine, int batch, int use_graph, void* stream);
@@ -146,6 +150,30 @@ int b200_engine_read_loss(void* engine, unsigned long long step, float* loss_hos
 int b200_engine_step_count(void* engine, unsigned long long* steps_host);
 /* kernels launched per train step at this batch size (for bench.py's gpu_launches) */
 int b200_engine_launches_per_step(void* engine, int batch, int* n_host);
+
+/* ---- symmetric memory + fused data-parallel reduction (mnist_ddp.py:173 DistributedDataParallel;
+ *      SURVEY N15, N17-N19, section 8 rows 11, 12, 15, 17) ---------------------------------------- */
+/* One device allocation per rank ([payload][barrier flags]), mapped into every peer with CUDA IPC. */
+int b200_symm_handle_bytes(void);
+int b200_symm_flag_bytes(void);
+int b200_symm_create(int world, int rank, size_t payload_bytes, void** arena_out);
+int b200_symm_export(void* arena, void* handle_out_host);            /* b200_symm_handle_bytes() bytes */
+int b200_symm_import(void* arena, const void* all_handles_host);      /* world handles, indexed by rank */
+int b200_symm_create_emulated(int world, size_t payload_bytes, void** arenas_out); /* W ranks on one GPU */
+int b200_symm_peer(void* arena, int rank, void** base_ptr);
+int b200_symm_pull(void* arena, int src_rank, size_t float_off, size_t n_floats, void* stream);
+int b200_symm_destroy(void* arena);
+/* A plan binds a bucket (float offsets inside the payload) to a barrier channel (0..3). */
+int b200_comm_plan_create(void* arena, size_t grad_off, size_t param_off, size_t v_off, size_t u_off,
+                          size_t n_floats, int channel, const void* ctrl, void** plan_out);
+int b200_comm_plan_create_emulated(void** arenas, int world, size_t grad_off, size_t param_off, size_t v_off,
+                                   size_t u_off, size_t n_floats, int channel, const void** ctrls, void** plan_out);
+int b200_comm_plan_destroy(void* plan);
+/* mode 0 one-shot / 1 two-shot; opt 1 = fused 1/W + Adadelta, 0 = averaged all-reduce into param_off;
+ * token 0 = derive from ctrl->step, else a caller token growing by 2 per call; nblocks 0 = automatic */
+int b200_comm_run(void* plan, int mode, int opt, unsigned int token, int nblocks, void* stream);
+/* engine created on the arena's buffers ([params][grads][sq_avg][acc_delta], ParamLayout.total floats each) */
+int b200_ddp_attach(void* engine, void* arena, int mode_bucket0, int mode_bucket1);
 
 #ifdef __cplusplus
 }

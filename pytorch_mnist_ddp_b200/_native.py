@@ -126,6 +126,21 @@ _SIGNATURES = {
     "b200_head_wgrad": [_vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp],
     "b200_eval_accumulate": [_vp, _vp, _i, _vp, _vp],
     "b200_adadelta": [_vp, _vp, _vp, _vp, _l, _vp, _f, _f, _i, _vp, _vp],
+    "b200_symm_create": [_i, _i, ctypes.c_size_t, ctypes.POINTER(_vp)],
+    "b200_symm_export": [_vp, _vp],
+    "b200_symm_import": [_vp, _vp],
+    "b200_symm_create_emulated": [_i, ctypes.c_size_t, ctypes.POINTER(_vp)],
+    "b200_symm_peer": [_vp, _i, ctypes.POINTER(_vp)],
+    "b200_symm_pull": [_vp, _i, ctypes.c_size_t, ctypes.c_size_t, _vp],
+    "b200_symm_destroy": [_vp],
+    "b200_comm_plan_create": [_vp, ctypes.c_size_t, ctypes.c_size_t, ctypes.c_size_t, ctypes.c_size_t,
+                              ctypes.c_size_t, _i, _vp, ctypes.POINTER(_vp)],
+    "b200_comm_plan_create_emulated": [ctypes.POINTER(_vp), _i, ctypes.c_size_t, ctypes.c_size_t, ctypes.c_size_t,
+                                       ctypes.c_size_t, ctypes.c_size_t, _i, ctypes.POINTER(_vp),
+                                       ctypes.POINTER(_vp)],
+    "b200_comm_plan_destroy": [_vp],
+    "b200_comm_run": [_vp, _i, _i, ctypes.c_uint, _i, _vp],
+    "b200_ddp_attach": [_vp, _vp, _i, _i],
     "b200_engine_create": [ctypes.POINTER(EngineConfig), ctypes.POINTER(_vp)],
     "b200_engine_destroy": [_vp],
     "b200_engine_buffer": [_vp, _i, ctypes.POINTER(_vp), ctypes.POINTER(ctypes.c_size_t)],
@@ -133,6 +148,8 @@ _SIGNATURES = {
     "b200_engine_begin_epoch": [_vp, _vp, _i, _vp],
     "b200_engine_set_lr": [_vp, _f, _vp],
     "b200_engine_set_dropout": [_vp, _i, _vp],
+    "b200_engine_set_defer_update": [_vp, _i],
+    "b200_engine_apply_update": [_vp, _i, _vp],
     "b200_engine_train_step": [_vp, _i, _i, _vp],
     "b200_engine_train_step_host": [_vp, _vp, _vp, _i, _i, _vp],
     "b200_engine_eval_batch": [_vp, _i, _i, _i, _vp],

@@ -218,8 +218,12 @@ class B200Backend:
         self.engine.load_data(0, train)
         self.engine.load_data(1, test)
         self.engine.set_state_dict(model.state_dict())
+        self._nccl_baseline = False
         if self.ddp is not None:
             self.ddp.attach(self.engine)  # broadcasts rank 0's parameters, installs the bucket hooks
+            if self.ddp.comm == "nccl":   # in-tree baseline: NCCL all-reduce + separate Adadelta kernel
+                self._nccl_baseline = True
+                N.check(self.engine.lib.b200_engine_set_defer_update(self.engine.handle, 1))
         self.engine.set_lr(lr)
         self._pinned_loss = torch.empty(64, dtype=torch.float32).pin_memory()
         self._slot = 0
@@ -232,6 +236,8 @@ class B200Backend:
     def train_step(self, step: int, batch: int, want_loss: bool = True):
         bsz = min(batch, self._epoch_n - step * batch)
         s = self.engine.train_step(bsz, self.use_graph)
+        if self._nccl_baseline:
+            self._nccl_reduce_and_update(bsz)
         if not want_loss:
             return None
         slot = self._slot
@@ -242,6 +248,16 @@ class B200Backend:
             ev = torch.cuda.Event()
             ev.record()
         return (slot, ev)
+
+    def _nccl_reduce_and_update(self, bsz: int) -> None:
+        """Reference-style reduction (mnist_ddp.py:173 via ncclAllReduce per bucket), then Adadelta."""
+        import torch.distributed as dist
+        eng = self.engine
+        with eng.on_stream():
+            for lo, hi in eng.layout.bucket_ranges:
+                dist.all_reduce(eng.grads[lo:hi], op=dist.ReduceOp.SUM)
+            eng.grads.mul_(1.0 / self.info.world_size)
+        N.check(eng.lib.b200_engine_apply_update(eng.handle, bsz, eng._s()))
 
     def loss(self, token) -> float:
         slot, ev = token

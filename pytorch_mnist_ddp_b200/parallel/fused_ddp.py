@@ -1,0 +1,180 @@
+"""Data parallelism without DistributedDataParallel: symmetric buffers + fused P2P kernels.
+
+What ``DistributedDataParallel(model, device_ids=[gpu])`` (mnist_ddp.py:173) sets up — parameter
+broadcast from rank 0, gradient buckets, an all-reduce per bucket overlapped with backward —
+is rebuilt here on top of csrc/symm.cu and csrc/allreduce.cu:
+
+* `SymmetricArena`: one device allocation per rank holding ``[params | grads | sq_avg | acc_delta]``
+  plus barrier flags, exported with CUDA IPC and mapped into every peer.  ``torch.distributed`` is
+  used for bootstrap only (all-gather of the 64-byte handles, barriers).
+* `FusedDataParallel.allocate()` hands the arena's buffers to the native engine, so backward
+  kernels write gradients straight into the peer-visible bucket (no bucket copy-in / copy-out).
+* `FusedDataParallel.attach()` pulls rank 0's parameters over NVLink (DDP's ``_sync_module_states``)
+  and installs the engine hooks that launch ONE fused all-reduce + 1/W + Adadelta kernel per
+  bucket: the fc bucket on a side stream while the conv backward still runs, the conv bucket at
+  the end (SURVEY N17 bucket layout; section 8 rows 11, 12, 15).
+
+Reduction modes (``--comm``): ``oneshot`` (every rank reduces the whole bucket), ``twoshot``
+(reduce-scatter + sharded Adadelta + parameter all-gather), ``auto`` = two-shot for the 4.7 MB fc
+bucket when world >= 4, one-shot otherwise.  ``nccl`` keeps the reference's unfused structure
+(ncclAllReduce + separate Adadelta) as the in-tree baseline.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Dict, List, Optional
+
+import torch
+import torch.distributed as dist
+
+from .. import _native as N
+from .dist import DistInfo
+
+ONESHOT, TWOSHOT = 0, 1
+
+
+class SymmetricArena:
+    """Peer-mapped device memory: ``payload_floats`` fp32 per rank + the barrier flag block."""
+
+    def __init__(self, handle: ctypes.c_void_p, world: int, rank: int, payload_floats: int) -> None:
+        self.handle, self.world, self.rank, self.payload_floats = handle, world, rank, payload_floats
+        self._views: Dict[int, torch.Tensor] = {}
+
+    @classmethod
+    def create(cls, info: DistInfo, payload_floats: int) -> "SymmetricArena":
+        lib = N.lib()
+        h = ctypes.c_void_p()
+        N.check(lib.b200_symm_create(info.world_size, info.rank, payload_floats * 4, ctypes.byref(h)))
+        arena = cls(h, info.world_size, info.rank, payload_floats)
+        if info.world_size > 1:
+            nb = lib.b200_symm_handle_bytes()
+            mine = (ctypes.c_char * nb)()
+            N.check(lib.b200_symm_export(h, mine))
+            dev = torch.device("cuda", torch.cuda.current_device())
+            local = torch.frombuffer(bytearray(mine.raw), dtype=torch.uint8).to(dev)
+            everyone = torch.empty(info.world_size * nb, dtype=torch.uint8, device=dev)
+            dist.all_gather_into_tensor(everyone, local)
+            blob = bytes(everyone.cpu().numpy().tobytes())
+            N.check(lib.b200_symm_import(h, blob))
+            dist.barrier()
+        return arena
+
+    @classmethod
+    def create_emulated(cls, world: int, payload_floats: int) -> List["SymmetricArena"]:
+        """`world` arenas on the current GPU, cross-linked like real ranks (single-GPU tests)."""
+        lib = N.lib()
+        hs = (ctypes.c_void_p * world)()
+        N.check(lib.b200_symm_create_emulated(world, payload_floats * 4, hs))
+        return [cls(ctypes.c_void_p(hs[r]), world, r, payload_floats) for r in range(world)]
+
+    def base_ptr(self, rank: Optional[int] = None) -> int:
+        p = ctypes.c_void_p()
+        N.check(N.lib().b200_symm_peer(self.handle, self.rank if rank is None else rank, ctypes.byref(p)))
+        return p.value
+
+    def view(self, rank: Optional[int] = None) -> torch.Tensor:
+        """The payload of a rank's arena as a flat fp32 tensor (peer views are real NVLink mappings)."""
+        from ..engine import _DevArray
+        r = self.rank if rank is None else rank
+        if r not in self._views:
+            arr = _DevArray(self.base_ptr(r), (self.payload_floats,), "<f4")
+            self._views[r] = torch.as_tensor(arr, device=f"cuda:{torch.cuda.current_device()}")
+        return self._views[r]
+
+    def destroy(self) -> None:
+        if self.handle:
+            N.lib().b200_symm_destroy(self.handle)
+            self.handle = None
+
+
+class CommPlan:
+    """One bucket bound to a barrier channel; `run` launches the fused kernel."""
+
+    def __init__(self, handle: ctypes.c_void_p) -> None:
+        self.handle = handle
+        self._token = 1
+
+    @classmethod
+    def create(cls, arena: SymmetricArena, grad_off: int, param_off: int, v_off: int, u_off: int, n: int,
+               channel: int, ctrl: Optional[torch.Tensor] = None) -> "CommPlan":
+        h = ctypes.c_void_p()
+        N.check(N.lib().b200_comm_plan_create(arena.handle, grad_off, param_off, v_off, u_off, n, channel,
+                                              None if ctrl is None else ctrl.data_ptr(), ctypes.byref(h)))
+        return cls(h)
+
+    @classmethod
+    def create_emulated(cls, arenas: List[SymmetricArena], grad_off: int, param_off: int, v_off: int, u_off: int,
+                        n: int, channel: int, ctrls: Optional[List[torch.Tensor]] = None) -> "CommPlan":
+        w = len(arenas)
+        hs = (ctypes.c_void_p * w)(*[a.handle for a in arenas])
+        cs = None
+        if ctrls is not None:
+            cs = (ctypes.c_void_p * w)(*[c.data_ptr() for c in ctrls])
+        h = ctypes.c_void_p()
+        N.check(N.lib().b200_comm_plan_create_emulated(hs, w, grad_off, param_off, v_off, u_off, n, channel, cs,
+                                                       ctypes.byref(h)))
+        return cls(h)
+
+    def run(self, mode: int, opt: bool, nblocks: int = 0, token: Optional[int] = None) -> None:
+        """token=None: use a private, monotonically increasing token; 0: derive from ctrl->step."""
+        if token is None:
+            token = self._token
+            self._token += 2
+        N.check(N.lib().b200_comm_run(self.handle, mode, int(opt), token, nblocks,
+                                      torch.cuda.current_stream().cuda_stream))
+
+    def destroy(self) -> None:
+        if self.handle:
+            N.lib().b200_comm_plan_destroy(self.handle)
+            self.handle = None
+
+
+class FusedDataParallel:
+    def __init__(self, info: DistInfo, comm: str = "auto") -> None:
+        if comm not in ("auto", "oneshot", "twoshot", "nccl", "nvls"):
+            raise ValueError(f"unknown comm mode {comm}")
+        if comm == "nvls":
+            raise N.NativeError("--comm nvls: multicast (NVLS) buffers are not wired up in this build; "
+                                "use twoshot (peer-to-peer reduce-scatter + parameter all-gather)")
+        self.info, self.comm = info, comm
+        w = info.world_size
+        if comm == "auto":
+            self.modes = (TWOSHOT if w >= 4 else ONESHOT, ONESHOT)
+        elif comm == "twoshot":
+            self.modes = (TWOSHOT, ONESHOT)
+        else:
+            self.modes = (ONESHOT, ONESHOT)
+        self.mode = {"auto": f"auto({'twoshot' if self.modes[0] else 'oneshot'}+oneshot)"}.get(comm, comm)
+        self.arena: Optional[SymmetricArena] = None
+        self.total = 0
+
+    def allocate(self, total_floats: int) -> Dict[str, int]:
+        """Create the arena and return the raw pointers the engine must use for its flat buffers."""
+        self.total = total_floats
+        self.arena = SymmetricArena.create(self.info, 4 * total_floats)
+        base = self.arena.base_ptr()
+        t = total_floats * 4
+        return {"params": base, "grads0": base + t, "grads1": base + t, "sq_avg": base + 2 * t,
+                "acc_delta": base + 3 * t}
+
+    def attach(self, engine) -> None:
+        lib = N.lib()
+        # DDP's _sync_module_states: every rank takes rank 0's parameters, pulled over NVLink
+        engine.synchronize()
+        dist.barrier()
+        N.check(lib.b200_symm_pull(self.arena.handle, 0, 0, self.total, engine._s()))
+        engine.synchronize()
+        dist.barrier()
+        if self.comm != "nccl":
+            N.check(lib.b200_ddp_attach(engine.handle, self.arena.handle, self.modes[0], self.modes[1]))
+        dist.barrier()
+
+    def verify_replicas(self) -> float:
+        """max |p_rank - p_rank0| over all parameters (should be exactly 0: fixed reduction order)."""
+        torch.cuda.synchronize()
+        dist.barrier()
+        mine = self.arena.view()[: self.total]
+        ref = self.arena.view(0)[: self.total]
+        d = (mine - ref).abs().max()
+        dist.all_reduce(d, op=dist.ReduceOp.MAX)
+        return float(d.item())

@@ -1,0 +1,89 @@
+"""torchrun worker for the multi-GPU data-parallel tests (launched by tests/test_gpu_comm.py).
+
+Checks, on real GPUs over NVLink:
+  1. W ranks x batch b with dropout off == 1 rank x batch W*b (loss and parameters after 3 steps);
+  2. every replica ends bit-identical to rank 0's (fixed reduction order / single owner per slice);
+  3. CUDA-graph replay of the step (with the side-stream all-reduce captured inside) works.
+"""
+import argparse
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--comm", default="auto")
+    ap.add_argument("--batch", type=int, default=64)
+    ap.add_argument("--steps", type=int, default=4)
+    args = ap.parse_args()
+    from pytorch_mnist_ddp_b200.engine import B200Backend, NativeEngine
+    from pytorch_mnist_ddp_b200.models.net import Net
+    from pytorch_mnist_ddp_b200.parallel.dist import DistInfo
+    from pytorch_mnist_ddp_b200.utils.data import synthetic_split
+
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", init_method="env://", world_size=world, rank=rank,
+                            device_id=torch.device("cuda", local))
+    info = DistInfo(True, rank, world, local, "nccl")
+    b, steps = args.batch, args.steps
+    train, test = synthetic_split(True, 4096), synthetic_split(False, 256)
+    g = torch.Generator().manual_seed(7)
+    perm = torch.randperm(len(train), generator=g)[: steps * world * b]
+    mine = torch.cat([perm[s * world * b + rank * b: s * world * b + (rank + 1) * b] for s in range(steps)])
+
+    torch.manual_seed(1)
+    backend = B200Backend(train, test, info, lr=1.0, seed=1, comm=args.comm, max_batch=world * b)
+    eng = backend.engine
+    eng.set_dropout(False)
+    eng.begin_epoch(mine.to(torch.int32))
+    for s in range(steps):
+        backend.train_step(s, b, want_loss=False)  # step 0 eager, step 1 captures the graph, then replays
+    eng.synchronize()
+    drift = backend.ddp.verify_replicas() if args.comm != "nccl" else 0.0
+    assert drift == 0.0, f"replicas drifted apart: max |p - p0| = {drift}"
+    losses = [eng.read_loss(s) for s in range(steps)]
+    lt = torch.tensor(losses, device="cuda", dtype=torch.float64)
+    dist.all_reduce(lt)
+    mean_losses = (lt / world).tolist()
+
+    ok = True
+    if rank == 0:
+        torch.manual_seed(1)
+        single = NativeEngine(world * b, len(train), len(test), seed=1)
+        single.load_data(0, train)
+        single.load_data(1, test)
+        init = Net().state_dict()
+        single.set_state_dict(init)
+        single.set_dropout(False)
+        single.begin_epoch(perm.to(torch.int32))
+        p_init = single.params.clone()
+        for s in range(steps):
+            st = single.train_step(world * b)
+            ref_loss = single.read_loss(st)
+            if abs(ref_loss - mean_losses[s]) > 2e-2 * max(1.0, abs(ref_loss)):
+                ok = False
+                print(f"step {s}: loss {mean_losses[s]} vs single-GPU {ref_loss}")
+        single.synchronize()
+        upd = (single.params - p_init).norm().item()
+        err = (single.params - eng.params).norm().item()
+        print(f"[{args.comm}] world {world}: update norm {upd:.5f}, DDP-vs-single error {err:.6f}, losses {mean_losses}")
+        if not err < 0.1 * upd:
+            ok = False
+        single.close()
+    flag = torch.tensor([1 if ok else 0], device="cuda")
+    dist.broadcast(flag, src=0)
+    dist.barrier()
+    if rank == 0 and flag.item() == 1:
+        print("DDP_EQUIVALENCE_OK")
+    dist.destroy_process_group()
+    sys.exit(0 if flag.item() == 1 else 1)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,111 @@
+"""Fused all-reduce (+ 1/W + Adadelta) kernels.
+
+On a single GPU the W ranks are emulated inside ONE cooperative launch (blockIdx.y = rank) over
+W cross-linked arenas, which exercises the same kernel code, flag protocol and fixed-order
+reduction as the real multi-GPU path.  The real NVLink path is covered by the multi-process
+tests at the bottom, which need >= 2 GPUs and are skipped otherwise.
+"""
+import os
+import subprocess
+import sys
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+# (floats) the two real DDP bucket sizes of this model rounded to the flat layout, plus
+# odd sizes: smaller than one CTA, not a multiple of the world size
+SIZES = [4, 1024, 18816, 19200, 1181184, 1048580]
+
+
+def _setup(world, n, seed=0):
+    from pytorch_mnist_ddp_b200.parallel.fused_ddp import SymmetricArena
+    arenas = SymmetricArena.create_emulated(world, 4 * n)
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    for a in arenas:
+        v = a.view()
+        v[:n] = torch.randn(n, device="cuda", generator=g)          # params / output
+        v[n:2 * n] = torch.randn(n, device="cuda", generator=g)     # grads
+        v[2 * n:] = 0                                               # Adadelta state
+    torch.cuda.synchronize()
+    return arenas
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+@pytest.mark.parametrize("mode", [0, 1])
+@pytest.mark.parametrize("n", SIZES)
+def test_allreduce_average_emulated(world, mode, n):
+    from pytorch_mnist_ddp_b200.parallel.fused_ddp import CommPlan
+    arenas = _setup(world, n)
+    grads = [a.view()[n:2 * n].clone() for a in arenas]
+    plan = CommPlan.create_emulated(arenas, n, 0, 2 * n, 3 * n, n, channel=2)
+    for rep in range(3):  # repeated calls reuse the flag words with growing tokens
+        plan.run(mode, opt=False)
+    torch.cuda.synchronize()
+    acc = torch.zeros(n, device="cuda")
+    for gq in grads:  # same fixed rank order, fp32: must match bit for bit
+        acc += gq
+    ref = acc * (1.0 / world)
+    outs = [a.view()[:n] for a in arenas]
+    for r in range(world):
+        assert torch.equal(outs[r], outs[0]), f"rank {r} differs from rank 0"
+    assert torch.equal(outs[0], ref)
+    ref64 = sum(gq.double() for gq in grads) / world
+    torch.testing.assert_close(outs[0].double(), ref64, rtol=1e-5, atol=1e-6)
+    plan.destroy()
+    for a in arenas:
+        a.destroy()
+
+
+@pytest.mark.parametrize("world", [2, 8])
+@pytest.mark.parametrize("mode", [0, 1])
+def test_fused_allreduce_adadelta_emulated(world, mode):
+    from pytorch_mnist_ddp_b200.ops import native_ops as ops
+    from pytorch_mnist_ddp_b200.parallel.fused_ddp import CommPlan
+    n = 19200
+    arenas = _setup(world, n, seed=3)
+    p0 = arenas[0].view()[:n].clone()
+    for a in arenas:  # replicas start identical, as after the initial broadcast
+        a.view()[:n] = p0
+    ctrls = [ops.make_ctrl(step=0, lr=1.0) for _ in range(world)]
+    plan = CommPlan.create_emulated(arenas, n, 0, 2 * n, 3 * n, n, channel=0, ctrls=ctrls)
+    ref_p = p0.clone().requires_grad_(True)
+    opt = torch.optim.Adadelta([ref_p], lr=1.0)
+    g = torch.Generator(device="cuda").manual_seed(5)
+    for step in range(5):
+        grads = [torch.randn(n, device="cuda", generator=g) * 0.01 for _ in range(world)]
+        for a, gq in zip(arenas, grads):
+            a.view()[n:2 * n] = gq
+        for c in ctrls:
+            c.copy_(ops.make_ctrl(step=step, lr=1.0))
+        torch.cuda.synchronize()
+        plan.run(mode, opt=True, token=0)  # token from ctrl->step, as in the engine
+        torch.cuda.synchronize()
+        acc = torch.zeros(n, device="cuda")
+        for gq in grads:
+            acc += gq
+        ref_p.grad = acc / world
+        opt.step()
+        for r in range(world):
+            assert torch.equal(arenas[r].view()[:n], arenas[0].view()[:n]), f"step {step}: rank {r} drifted"
+        torch.testing.assert_close(arenas[0].view()[:n], ref_p.detach(), rtol=1e-4, atol=1e-5)
+    plan.destroy()
+    for a in arenas:
+        a.destroy()
+
+
+def _torchrun(nproc, script_args, timeout=600):
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}",
+           "--master-addr", "127.0.0.1", "--master-port", "29533"] + script_args
+    return subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=timeout)
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs >= 2 GPUs")
+@pytest.mark.parametrize("comm", ["oneshot", "twoshot"])
+def test_multi_gpu_ddp_equivalence(comm):
+    """2 ranks x batch b without dropout == 1 rank x batch 2b ('DDP equivalence')."""
+    res = _torchrun(2, ["tests/ddp_worker.py", "--comm", comm])
+    assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
+    assert "DDP_EQUIVALENCE_OK" in res.stdout, res.stdout[-3000:]
