@@ -1,0 +1,240 @@
+"""CPU-only tests (no GPU needed): sampler parity, data, layouts, log formats, CLI, checkpoints,
+the plain-torch backend, 2-process gloo data parallelism, and trajectory parity with the unmodified
+reference script on the CPU."""
+import io
+import os
+import re
+import subprocess
+import sys
+from contextlib import redirect_stdout
+
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REF = "/root/reference"
+
+
+# ---------------------------------------------------------------------------------------------
+# samplers
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("world", [1, 2, 4, 8, 7])
+@pytest.mark.parametrize("epoch", [1, 2, 20])
+def test_distributed_indices_equal_torch_distributed_sampler(world, epoch):
+    from torch.utils.data.distributed import DistributedSampler
+    from pytorch_mnist_ddp_b200.parallel.sampler import distributed_indices
+    n = 60000 if world != 7 else 1003  # 7 does not divide: exercises the wrap-around padding
+    ds = list(range(n))
+    for rank in {0, world - 1}:
+        s = DistributedSampler(ds, num_replicas=world, rank=rank, shuffle=True)
+        s.set_epoch(epoch)
+        assert distributed_indices(n, world, rank, epoch).tolist() == list(iter(s))
+
+
+def test_distributed_sampler_goldens_from_survey():
+    # SURVEY A.3
+    from pytorch_mnist_ddp_b200.parallel.sampler import distributed_indices
+    assert distributed_indices(60000, 1, 0, 1)[:8].tolist() == [35845, 27522, 33254, 23645, 11299, 16178, 58355, 27002]
+    assert distributed_indices(60000, 8, 0, 1)[:8].tolist() == [35845, 35815, 17862, 7131, 46903, 46045, 36401, 17575]
+    r7 = distributed_indices(60000, 8, 7, 1)
+    assert r7[:8].tolist() == [27002, 16665, 1176, 46194, 30794, 52889, 36743, 24548] and r7.numel() == 7500
+
+
+def test_random_indices_follow_random_sampler_stream():
+    from torch.utils.data import RandomSampler
+    from pytorch_mnist_ddp_b200.parallel.sampler import random_indices
+    torch.manual_seed(123)
+    ref = list(iter(RandomSampler(list(range(1000)))))
+    torch.manual_seed(123)
+    assert random_indices(1000).tolist() == ref
+
+
+def test_steps_per_epoch_table():
+    # SURVEY 3.3 table
+    from pytorch_mnist_ddp_b200.utils.data import split_sizes
+    assert split_sizes(60000, 1, 64)[1] == 938 and split_sizes(60000, 8, 200)[1] == 38
+    assert split_sizes(60000, 4, 200) == (15000, 75) and split_sizes(60000, 8, 4096)[1] == 2
+
+
+# ---------------------------------------------------------------------------------------------
+# data, layout, formats
+# ---------------------------------------------------------------------------------------------
+def test_idx_roundtrip_and_torchvision_compat(tmp_path):
+    from pytorch_mnist_ddp_b200.utils import data
+    tr, te = data.synthetic_split(True, 64), data.synthetic_split(False, 32)
+    data.write_idx_files(str(tmp_path), tr, te)
+    back = data.load_split(str(tmp_path), True)
+    assert not back.synthetic and torch.equal(back.images, tr.images) and torch.equal(back.labels, tr.labels)
+    from torchvision import datasets
+    tv = datasets.MNIST(str(tmp_path), train=False, download=False)  # the parser the reference uses
+    assert torch.equal(tv.data, te.images) and torch.equal(tv.targets, te.labels.long())
+
+
+def test_normalize_batch_matches_torchvision_transform():
+    from torchvision import transforms
+    from PIL import Image
+    from pytorch_mnist_ddp_b200.utils.data import normalize_batch, synthetic_split
+    s = synthetic_split(True, 8)
+    t = transforms.Compose([transforms.ToTensor(), transforms.Normalize((0.1307,), (0.3081,))])
+    ref = torch.stack([t(Image.fromarray(img.numpy(), mode="L")) for img in s.images])
+    assert torch.equal(normalize_batch(s.images), ref)
+
+
+def test_param_layout_roundtrip_and_buckets():
+    from pytorch_mnist_ddp_b200.models.net import NUM_PARAMS, Net, ParamLayout
+    torch.manual_seed(1)
+    net = Net()
+    lay = ParamLayout()
+    assert sum(p.numel() for p in net.parameters()) == NUM_PARAMS == 1_199_882
+    assert lay.real_bucket_bytes() == [4_724_264, 75_264]  # DDP's rebuilt buckets
+    assert lay.total % 256 == 0 and all(seg.offset % 256 == 0 for seg in lay.segments.values())
+    flat = lay.pack(net.state_dict())
+    back = lay.unpack(flat)
+    for k, v in net.state_dict().items():
+        assert torch.equal(back[k], v), k
+    # fc1 is stored with the 9216 axis in (h, w, c) order: applying it to an NHWC-flattened input must agree
+    x = torch.randn(2, 64, 12, 12)
+    seg = lay.segments["fc1.weight"]
+    w_int = flat[seg.offset: seg.offset + seg.numel].view(128, 9216)
+    torch.testing.assert_close(x.permute(0, 2, 3, 1).reshape(2, -1) @ w_int.t(),
+                               x.reshape(2, -1) @ net.fc1.weight.t(), rtol=1e-5, atol=1e-5)
+    # seed-1 init sums
+    assert abs(net.conv1.weight.double().sum().item() - 3.680015) < 1e-5
+    assert abs(net.fc1.weight.double().sum().item() + 2.565831) < 1e-5
+
+
+def test_forward_golden_from_survey():
+    # RNG-free input, eval mode, seed-1 init
+    from pytorch_mnist_ddp_b200.models.net import Net
+    torch.manual_seed(1)
+    net = Net().double().eval()
+    n, h, w = torch.meshgrid(torch.arange(8), torch.arange(28), torch.arange(28), indexing="ij")
+    raw = ((131 * n + 17 * h + 29 * w) % 256).double()
+    x = ((raw / 255 - 0.1307) / 0.3081).unsqueeze(1)
+    y = torch.arange(8) % 10
+    loss = torch.nn.functional.nll_loss(net(x), y)
+    assert abs(loss.item() - 2.3127241799) < 1e-6
+
+
+def test_log_formats_byte_for_byte():
+    from pytorch_mnist_ddp_b200.utils import logfmt
+    assert logfmt.train_line(1, 640, 60000, 10, 938, 2.301234) == "Train Epoch: 1 [640/60000 (1%)]\tLoss: 2.301234"
+    assert logfmt.test_line(2.3032, 988, 10000) == "\nTest set: Average loss: 2.3032, Accuracy: 988/10000 (10%)\n"
+    assert logfmt.banner(3, "env://", 1, 4) == "| distributed init (rank 3): env://, local rank:1, world size:4"
+    assert logfmt.total_time_line(1.5) == "Total cost time:1.5 ms"
+
+
+def test_cli_flags_match_reference():
+    from pytorch_mnist_ddp_b200.cli import build_parser
+    a = build_parser(True).parse_args([])
+    assert (a.batch_size, a.test_batch_size, a.epochs, a.lr, a.gamma, a.seed, a.log_interval) == (64, 1000, 14, 1.0, 0.7, 1, 10)
+    assert not (a.no_cuda or a.dry_run or a.save_model) and a.world_size == 1 and a.dist_url == "env://"
+    # both spellings of the launcher-provided flag
+    assert build_parser(True).parse_args(["--local_rank", "2"]).local_rank == 2
+    assert build_parser(True).parse_args(["--local-rank=3"]).local_rank == 3
+    with pytest.raises(SystemExit):
+        build_parser(False).parse_args(["--world-size", "2"])  # mnist.py has no DDP flags
+
+
+def test_checkpoint_reference_format(tmp_path):
+    from pytorch_mnist_ddp_b200.models.net import Net, PARAM_SPECS
+    from pytorch_mnist_ddp_b200.utils import checkpoint
+    torch.manual_seed(1)
+    net = Net()
+    p = str(tmp_path / "mnist_cnn.pt")
+    checkpoint.save(net.state_dict(), p, prefix="module.")
+    raw = torch.load(p, weights_only=True)
+    assert list(raw) == ["module." + k for k in PARAM_SPECS]
+    assert 4_790_000 < os.path.getsize(p) < 4_820_000  # 4,803,113 B for the reference's file
+    loaded = checkpoint.load(p)
+    net2 = Net()
+    net2.load_state_dict(loaded)
+    assert all(torch.equal(a, b) for a, b in zip(net.state_dict().values(), net2.state_dict().values()))
+
+
+def test_native_library_builds_for_sm100a():
+    from pytorch_mnist_ddp_b200 import _native
+    lib = _native.lib()
+    assert lib.b200_version() >= 100 and lib.b200_has_tc() == 1
+    out = subprocess.run(["cuobjdump", "-lelf", _native.LIBPATH], capture_output=True, text=True).stdout
+    assert "sm_100a" in out and "sm_90" not in out
+
+
+# ---------------------------------------------------------------------------------------------
+# plain-torch backend end to end (tiny dataset through the real CLI code path)
+# ---------------------------------------------------------------------------------------------
+def _tiny_root(tmp_path, n_train=256, n_test=64):
+    from pytorch_mnist_ddp_b200.utils import data
+    data.write_idx_files(str(tmp_path), data.synthetic_split(True, n_train), data.synthetic_split(False, n_test))
+    return str(tmp_path)
+
+
+def test_cli_single_process_cpu_run(tmp_path, monkeypatch):
+    from pytorch_mnist_ddp_b200.cli import main_single
+    root = _tiny_root(tmp_path)
+    monkeypatch.chdir(tmp_path)
+    buf = io.StringIO()
+    with redirect_stdout(buf):
+        main_single(["--no-cuda", "--epochs", "2", "--batch-size", "32", "--test-batch-size", "64", "--log-interval", "4",
+                     "--data-root", root, "--save-model"])
+    out = buf.getvalue()
+    lines = [l for l in out.splitlines() if l.startswith("Train Epoch")]
+    assert len(lines) == 4 and lines[0].startswith("Train Epoch: 1 [0/256 (0%)]\tLoss: ")
+    assert lines[1].startswith("Train Epoch: 1 [128/256 (50%)]")
+    assert len(re.findall(r"Test set: Average loss: \d+\.\d{4}, Accuracy: \d+/64 \(\d+%\)", out)) == 2
+    sd = torch.load(str(tmp_path / "mnist_cnn.pt"), weights_only=True)
+    assert list(sd)[0] == "conv1.weight"
+
+
+def test_cli_ddp_script_non_distributed_cpu(tmp_path, monkeypatch):
+    from pytorch_mnist_ddp_b200.cli import main_ddp
+    root = _tiny_root(tmp_path)
+    monkeypatch.chdir(tmp_path)
+    for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK", "SLURM_PROCID"):
+        monkeypatch.delenv(k, raising=False)
+    buf = io.StringIO()
+    with redirect_stdout(buf):
+        main_ddp(["--no-cuda", "--epochs", "1", "--batch-size", "64", "--dry-run", "--data-root", root, "--save-model"])
+    out = buf.getvalue()
+    assert out.startswith("Not using distributed mode\n")
+    assert out.count("Train Epoch") == 1 and "Total cost time:" in out and out.rstrip().endswith(" ms")
+    assert os.path.isfile(tmp_path / "mnist_cnn_.pt")  # the reference's non-distributed file name
+
+
+def test_gloo_two_process_ddp_matches_single_process(tmp_path):
+    """2 ranks x batch 32 == 1 rank x batch 64 for the torch backend (dropout disabled via eval-mode hack
+    is not available through the CLI, so compare the first step's loss and the shard bookkeeping)."""
+    root = _tiny_root(tmp_path, 256, 64)
+    env = dict(os.environ, PYTHONPATH=ROOT, OMP_NUM_THREADS="1")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr",
+           "127.0.0.1", "--master-port", "29641", os.path.join(ROOT, "mnist_ddp.py"), "--no-cuda", "--epochs", "1",
+           "--batch-size", "32", "--test-batch-size", "64", "--log-interval", "1", "--data-root", root, "--save-model"]
+    res = subprocess.run(cmd, cwd=str(tmp_path), env=env, capture_output=True, text=True, timeout=600)
+    assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-2000:]
+    out = res.stdout
+    assert out.count("| distributed init (rank ") == 2 and "world size:2" in out
+    trains = [l for l in out.splitlines() if l.startswith("Train Epoch")]
+    assert len(trains) == 4  # 128 samples per rank / 32, printed by rank 0 only
+    assert trains[1].startswith("Train Epoch: 1 [64/256 (25%)]")  # world * batch_idx * len(data)
+    assert out.count("Test set: Average loss") == 1  # rank 0 only
+    assert out.count("Total cost time:") == 2        # every rank
+    sd = torch.load(str(tmp_path / "mnist_cnn.pt"), weights_only=True)
+    assert list(sd)[0] == "module.conv1.weight"      # DDP-wrapper key prefix kept for compatibility
+
+
+@pytest.mark.slow
+@pytest.mark.skipif(not os.path.isfile(os.path.join(REF, "mnist.py")), reason="reference checkout not present")
+def test_cpu_trajectory_is_bit_identical_to_reference_script(tmp_path):
+    """Same seed, same idx files: our --no-cuda path must print exactly the reference's loss values."""
+    from pytorch_mnist_ddp_b200.utils import data
+    root = tmp_path / "data"
+    data.write_idx_files(str(root), data.synthetic_split(True, 60000), data.synthetic_split(False, 10000))
+    env = dict(os.environ, PYTHONPATH=ROOT)
+    args = ["--no-cuda", "--epochs", "1", "--batch-size", "64", "--dry-run"]
+    ref = subprocess.run([sys.executable, os.path.join(REF, "mnist.py")] + args, cwd=str(tmp_path), env=env,
+                         capture_output=True, text=True, timeout=900)
+    ours = subprocess.run([sys.executable, os.path.join(ROOT, "mnist.py")] + args + ["--data-root", str(root)],
+                          cwd=str(tmp_path), env=env, capture_output=True, text=True, timeout=900)
+    assert ref.returncode == 0 and ours.returncode == 0, ref.stderr[-1500:] + ours.stderr[-1500:]
+    pick = lambda s: [l for l in s.splitlines() if l.startswith(("Train Epoch", "Test set"))]
+    assert pick(ours.stdout) == pick(ref.stdout), (pick(ours.stdout), pick(ref.stdout))
