@@ -63,7 +63,9 @@ int enqueue_forward(Engine* E, const uint8_t* images, const uint8_t* labels, con
   const B200EngineConfig& c = E->cfg;
   float* P = E->P;
   TRY(b200_conv1_fwd(images, idx, ctrl, P + c.offsets[0], P + c.offsets[1], E->a1, batch, s));
-  if (E->use_tc & B200_TC_CONV2_FWD)
+  if ((E->use_tc & B200_TC_CONV2_FWD) && (E->use_tc & B200_TC_CONV2_V2))
+    TRY(b200_conv2_fwd_tc2(E->a1, P + c.offsets[2], P + c.offsets[3], ctrl, E->pooled, E->amax, batch, s));
+  else if (E->use_tc & B200_TC_CONV2_FWD)
     TRY(b200_conv2_fwd_tc(E->a1, P + c.offsets[2], P + c.offsets[3], ctrl, E->pooled, E->amax, batch, s));
   else
     TRY(b200_conv2_fwd_simt(E->a1, P + c.offsets[2], P + c.offsets[3], ctrl, E->pooled, E->amax, batch, s));
@@ -102,8 +104,13 @@ int enqueue_train(Engine* E, const uint8_t* images, const uint8_t* labels, const
   if (E->hooks.bucket_ready) TRY(E->hooks.bucket_ready(E, 0, s));
   if (E->use_tc & B200_TC_CONV2_BWD) {
     TRY(b200_unpool_dense(E->dp, E->amax, E->dy, E->db_part, G + c.offsets[3], batch, s));
-    TRY(b200_conv2_wgrad_tc(E->dy, E->a1, E->c2_part, G + c.offsets[2], batch, s));
-    TRY(b200_conv2_dgrad_tc(E->dy, P + c.offsets[2], E->a1, E->da1, batch, s));
+    if (E->use_tc & B200_TC_CONV2_V2) {
+      TRY(b200_conv2_wgrad_tc2(E->dy, E->a1, E->c2_part, G + c.offsets[2], batch, s));
+      TRY(b200_conv2_dgrad_tc2(E->dy, P + c.offsets[2], E->a1, E->da1, batch, s));
+    } else {
+      TRY(b200_conv2_wgrad_tc(E->dy, E->a1, E->c2_part, G + c.offsets[2], batch, s));
+      TRY(b200_conv2_dgrad_tc(E->dy, P + c.offsets[2], E->a1, E->da1, batch, s));
+    }
   } else {
     TRY(b200_conv2_wgrad_simt(E->dp, E->amax, E->a1, E->c2_part, G + c.offsets[2], G + c.offsets[3], batch, s));
     TRY(b200_conv2_dgrad_simt(E->dp, E->amax, P + c.offsets[2], E->a1, E->da1, batch, s));

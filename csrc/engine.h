@@ -6,7 +6,7 @@
 
 #include "common.cuh"
 
-enum { B200_TC_CONV2_FWD = 1, B200_TC_FC1_FWD = 2, B200_TC_FC1_BWD = 4, B200_TC_CONV2_BWD = 8 };
+enum { B200_TC_CONV2_FWD = 1, B200_TC_FC1_FWD = 2, B200_TC_FC1_BWD = 4, B200_TC_CONV2_BWD = 8, B200_TC_CONV2_V2 = 16 };
 
 struct Engine;
 struct EngineHooks {

@@ -112,6 +112,15 @@ __device__ __forceinline__ uint64_t smem_desc(uint32_t saddr, uint32_t lbo_bytes
 __device__ __forceinline__ uint64_t desc_kmajor(uint32_t saddr) { return smem_desc(saddr, 16, 1024, 2); }
 // MN-major tf32 operand: 32-element chunks `lbo` bytes apart, 4-k-row atoms 512 B apart
 __device__ __forceinline__ uint64_t desc_mnmajor(uint32_t saddr, uint32_t lbo) { return smem_desc(saddr, lbo, 512, 1); }
+// Views into a larger TMA-written buffer.  MEASURED on B200: the tensor core applies the swizzle XOR
+// to the absolute shared-memory address bits (exactly like TMA does when it writes), so a descriptor
+// may start any whole number of 128-byte rows into a swizzled buffer and its 8-row groups may be any
+// multiple of 1024 bytes apart — the base-offset field stays 0 (setting it to the start row's phase
+// gives wrong results).  This is what turns a 3x3 convolution tap into a mere address offset.
+__device__ __forceinline__ uint64_t desc_kmajor_view(uint32_t saddr, uint32_t sbo) { return smem_desc(saddr, 16, sbo, 2); }
+__device__ __forceinline__ uint64_t desc_mnmajor_view(uint32_t saddr, uint32_t lbo, uint32_t sbo) {
+  return smem_desc(saddr, lbo, sbo, 1);
+}
 
 // instruction descriptor: kind::tf32, fp32 accumulate, dense
 __host__ __device__ constexpr uint32_t idesc_tf32(int M, int N, int a_mn, int b_mn) {

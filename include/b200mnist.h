@@ -81,6 +81,11 @@ int b200_tc_gemm(const float* A, const float* B, float* D, int M, int N, int K, 
 /* implicit-GEMM conv2 forward with the fused bias+ReLU+pool+dropout epilogue (same outputs as _simt) */
 int b200_conv2_fwd_tc(const float* a1, const float* w, const float* bias, const void* ctrl, float* pooled,
                       uint8_t* amax, int batch, void* stream);
+/* second generation: one TMA patch load per (image, half), taps as shifted descriptor views */
+int b200_conv2_fwd_tc2(const float* a1, const float* w, const float* bias, const void* ctrl, float* pooled,
+                       uint8_t* amax, int batch, void* stream);
+int b200_conv2_dgrad_tc2(const float* dy, const float* w, const float* a1, float* da1, int batch, void* stream);
+int b200_conv2_wgrad_tc2(const float* dy, const float* a1, float* part, float* dw, int batch, void* stream);
 /* implicit-GEMM dgrad from the dense dY [B][24][24][64]; epilogue applies conv1's ReLU mask */
 int b200_conv2_dgrad_tc(const float* dy, const float* w, const float* a1, float* da1, int batch, void* stream);
 /* implicit-GEMM wgrad from the dense dY; part as for _simt; the bias gradient comes from b200_unpool_dense */
@@ -105,7 +110,8 @@ typedef struct B200EngineConfig {
   int max_batch;        /* largest train or eval batch that will be used */
   int world, rank;
   unsigned long long seed;
-  int use_tc;           /* 1: tcgen05 kernels for conv2/fc1; 0: CUDA-core kernels everywhere */
+  int use_tc;           /* bit mask: 1 conv2 fwd, 2 fc1 fwd, 4 fc1 bwd, 8 conv2 bwd on tcgen05; 16: patch-view (v2)
+                           conv2 kernels; 0: CUDA-core kernels everywhere */
   int train_n, test_n;  /* dataset sizes (samples) */
   long param_floats;    /* ParamLayout.total */
   long offsets[8];      /* conv1.w, conv1.b, conv2.w, conv2.b, fc1.w, fc1.b, fc2.w, fc2.b (floats) */

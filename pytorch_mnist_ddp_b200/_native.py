@@ -120,6 +120,9 @@ _SIGNATURES = {
     "b200_sgemm": [_vp, _l, _l, _vp, _l, _l, _vp, _i, _i, _i, _i, _i, _vp, _f, _vp],
     "b200_tc_gemm": [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp, _f, _vp],
     "b200_conv2_fwd_tc": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _vp],
+    "b200_conv2_fwd_tc2": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _vp],
+    "b200_conv2_dgrad_tc2": [_vp, _vp, _vp, _vp, _i, _vp],
+    "b200_conv2_wgrad_tc2": [_vp, _vp, _vp, _vp, _i, _vp],
     "b200_conv2_dgrad_tc": [_vp, _vp, _vp, _vp, _i, _vp],
     "b200_conv2_wgrad_tc": [_vp, _vp, _vp, _vp, _i, _vp],
     "b200_head_fused": [_vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp],

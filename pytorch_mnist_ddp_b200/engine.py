@@ -29,8 +29,8 @@ from .utils.data import MnistSplit
  BUF_DLOGITS, BUF_DH, BUF_DP, BUF_DA1, BUF_LOSS_I, BUF_LOSS_RING, BUF_CTRL, BUF_LOGP, BUF_STAGE_IMG,
  BUF_STAGE_LBL, BUF_FC1_PART) = range(20)
 LOSS_RING = 1024
-TC_CONV2_FWD, TC_FC1_FWD, TC_FC1_BWD, TC_CONV2_BWD = 1, 2, 4, 8
-TC_ALL = 15
+TC_CONV2_FWD, TC_FC1_FWD, TC_FC1_BWD, TC_CONV2_BWD, TC_CONV2_V2 = 1, 2, 4, 8, 16
+TC_ALL = 31
 DEFAULT_TC = TC_ALL
 
 

@@ -61,7 +61,8 @@ def conv2_fwd(a1: torch.Tensor, w: torch.Tensor, b: torch.Tensor, ctrl: torch.Te
     batch = a1.shape[0]
     pooled = torch.empty(batch, 12, 12, 64, device="cuda")
     amax = torch.empty(batch, 12, 12, 64, dtype=torch.uint8, device="cuda")
-    fn = N.lib().b200_conv2_fwd_tc if tc else N.lib().b200_conv2_fwd_simt
+    L = N.lib()
+    fn = L.b200_conv2_fwd_tc2 if tc == 2 else (L.b200_conv2_fwd_tc if tc else L.b200_conv2_fwd_simt)
     N.check(fn(_p(a1), _p(w), _p(b), _p(ctrl), _p(pooled), _p(amax), batch, _s()))
     return pooled, amax
 
@@ -84,7 +85,8 @@ def conv2_dgrad(dp, amax, w, a1, tc: bool = False) -> torch.Tensor:
     da1 = torch.empty(batch, 26, 26, 32, device="cuda")
     if tc:
         dy = unpool_dense(dp, amax)
-        N.check(N.lib().b200_conv2_dgrad_tc(_p(dy), _p(w), _p(a1), _p(da1), batch, _s()))
+        fn = N.lib().b200_conv2_dgrad_tc2 if tc == 2 else N.lib().b200_conv2_dgrad_tc
+        N.check(fn(_p(dy), _p(w), _p(a1), _p(da1), batch, _s()))
     else:
         N.check(N.lib().b200_conv2_dgrad_simt(_p(dp), _p(amax), _p(w), _p(a1), _p(da1), batch, _s()))
     return da1
@@ -97,7 +99,8 @@ def conv2_wgrad(dp, amax, a1, tc: bool = False) -> Tuple[torch.Tensor, torch.Ten
     dw, db = torch.empty(9, 64, 32, device="cuda"), torch.empty(64, device="cuda")
     if tc:
         dy, db = unpool_dense(dp, amax, with_db=True)
-        N.check(L.b200_conv2_wgrad_tc(_p(dy), _p(a1), _p(part), _p(dw), batch, _s()))
+        fn = L.b200_conv2_wgrad_tc2 if tc == 2 else L.b200_conv2_wgrad_tc
+        N.check(fn(_p(dy), _p(a1), _p(part), _p(dw), batch, _s()))
     else:
         N.check(L.b200_conv2_wgrad_simt(_p(dp), _p(amax), _p(a1), _p(part), _p(dw), _p(db), batch, _s()))
     return dw, db

@@ -39,6 +39,8 @@ class SymmetricArena:
     def __init__(self, handle: ctypes.c_void_p, world: int, rank: int, payload_floats: int) -> None:
         self.handle, self.world, self.rank, self.payload_floats = handle, world, rank, payload_floats
         self._views: Dict[int, torch.Tensor] = {}
+        # barrier tokens must keep growing per channel across ALL plans that share the flag words
+        self.tokens: Dict[int, int] = {}
 
     @classmethod
     def create(cls, info: DistInfo, payload_floats: int) -> "SymmetricArena":
@@ -90,9 +92,8 @@ class SymmetricArena:
 class CommPlan:
     """One bucket bound to a barrier channel; `run` launches the fused kernel."""
 
-    def __init__(self, handle: ctypes.c_void_p) -> None:
-        self.handle = handle
-        self._token = 1
+    def __init__(self, handle: ctypes.c_void_p, arena: "SymmetricArena", channel: int) -> None:
+        self.handle, self.arena, self.channel = handle, arena, channel
 
     @classmethod
     def create(cls, arena: SymmetricArena, grad_off: int, param_off: int, v_off: int, u_off: int, n: int,
@@ -100,7 +101,7 @@ class CommPlan:
         h = ctypes.c_void_p()
         N.check(N.lib().b200_comm_plan_create(arena.handle, grad_off, param_off, v_off, u_off, n, channel,
                                               None if ctrl is None else ctrl.data_ptr(), ctypes.byref(h)))
-        return cls(h)
+        return cls(h, arena, channel)
 
     @classmethod
     def create_emulated(cls, arenas: List[SymmetricArena], grad_off: int, param_off: int, v_off: int, u_off: int,
@@ -113,13 +114,13 @@ class CommPlan:
         h = ctypes.c_void_p()
         N.check(N.lib().b200_comm_plan_create_emulated(hs, w, grad_off, param_off, v_off, u_off, n, channel, cs,
                                                        ctypes.byref(h)))
-        return cls(h)
+        return cls(h, arenas[0], channel)
 
     def run(self, mode: int, opt: bool, nblocks: int = 0, token: Optional[int] = None) -> None:
         """token=None: use a private, monotonically increasing token; 0: derive from ctrl->step."""
         if token is None:
-            token = self._token
-            self._token += 2
+            token = self.arena.tokens.get(self.channel, 1)
+            self.arena.tokens[self.channel] = token + 2
         N.check(N.lib().b200_comm_run(self.handle, mode, int(opt), token, nblocks,
                                       torch.cuda.current_stream().cuda_stream))
 

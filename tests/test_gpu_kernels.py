@@ -70,7 +70,7 @@ def test_conv1_fwd_gather_normalize(ops, batch):
 
 
 @pytest.mark.parametrize("batch", BATCHES)
-@pytest.mark.parametrize("tc", [False, True])
+@pytest.mark.parametrize("tc", [False, True, 2])
 def test_conv2_fwd_eval(ops, batch, tc):
     _need_tc(tc)
     net = _net()
@@ -89,7 +89,7 @@ def test_conv2_fwd_eval(ops, batch, tc):
     torch.testing.assert_close(picked[live], ref[live], **tol)
 
 
-@pytest.mark.parametrize("tc", [False, True])
+@pytest.mark.parametrize("tc", [False, True, 2])
 def test_conv2_fwd_dropout(ops, tc):
     _need_tc(tc)
     net = _net()
@@ -193,7 +193,7 @@ def test_head_eval_and_train(ops, batch):
 
 
 @pytest.mark.parametrize("batch", [1, 7, 64])
-@pytest.mark.parametrize("tc", [False, True])
+@pytest.mark.parametrize("tc", [False, True, 2])
 def test_conv2_backward(ops, batch, tc):
     _need_tc(tc)
     net = _net()
