@@ -71,9 +71,10 @@ conv2_fwd_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_const
   const int my_tiles = (ntiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
 
   if (warp == 0) {
-    if (lane == 0) {
-      mbar_expect_tx(&w_bar, 9 * TAP_BYTES);
-      for (int t = 0; t < 9; ++t) tma_load_2d(wsm + t * TAP_BYTES, &mapW, &w_bar, 0, t * 64);
+    {
+      const bool leader = elect_one();  // whole warp stays convergent: operands live in uniform registers
+      if (leader) mbar_expect_tx(&w_bar, 9 * TAP_BYTES);
+      for (int t = 0; t < 9; ++t) if (leader) tma_load_2d(wsm + t * TAP_BYTES, &mapW, &w_bar, 0, t * 64);
       int g = 0;
       for (int it = 0; it < my_tiles; ++it) {
         const int tile = blockIdx.x + it * gridDim.x;
@@ -81,13 +82,14 @@ conv2_fwd_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_const
         for (int tap = 0; tap < 9; ++tap, ++g) {
           const int s = g % F_STAGES;
           mbar_wait(&empty_bar[s], ((g / F_STAGES) & 1) ^ 1);
-          mbar_expect_tx(&full_bar[s], F_A_BYTES);
-          tma_load_4d(asm_ + s * F_A_BYTES, &mapA, &full_bar[s], 0, bx + tap % 3, by + tap / 3, pair * 2);
+          if (leader) mbar_expect_tx(&full_bar[s], F_A_BYTES);
+          if (leader) tma_load_4d(asm_ + s * F_A_BYTES, &mapA, &full_bar[s], 0, bx + tap % 3, by + tap / 3, pair * 2);
         }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    {
+      const bool leader = elect_one();  // whole warp stays convergent: operands live in uniform registers
       constexpr uint32_t idesc = idesc_tf32(128, 64, 0, 0);
       mbar_wait(&w_bar, 0);
       int g = 0;
@@ -103,10 +105,10 @@ conv2_fwd_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_const
           const uint32_t sa = smem_u32(asm_ + s * F_A_BYTES), sw = smem_u32(wsm + tap * TAP_BYTES);
 #pragma unroll
           for (int kk = 0; kk < 4; ++kk)
-            umma_tf32(d, desc_kmajor(sa + kk * 32), desc_kmajor(sw + kk * 32), idesc, (tap | kk) != 0);
-          umma_commit(&empty_bar[s]);
+            if (leader) umma_tf32(d, desc_kmajor(sa + kk * 32), desc_kmajor(sw + kk * 32), idesc, (tap | kk) != 0);
+          if (leader) umma_commit(&empty_bar[s]);
         }
-        umma_commit(&tfull_bar[acc]);
+        if (leader) umma_commit(&tfull_bar[acc]);
       }
     }
   } else {
@@ -232,9 +234,10 @@ conv2_dgrad_tc_kernel(const __grid_constant__ CUtensorMap mapDY, const __grid_co
   const int my_tiles = (ntiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
 
   if (warp == 0) {
-    if (lane == 0) {
-      mbar_expect_tx(&w_bar, 9 * TAP_BYTES);
-      for (int t = 0; t < 9; ++t) tma_load_2d(wsm + t * TAP_BYTES, &mapW, &w_bar, 0, t * 64);
+    {
+      const bool leader = elect_one();  // whole warp stays convergent: operands live in uniform registers
+      if (leader) mbar_expect_tx(&w_bar, 9 * TAP_BYTES);
+      for (int t = 0; t < 9; ++t) if (leader) tma_load_2d(wsm + t * TAP_BYTES, &mapW, &w_bar, 0, t * 64);
       int g = 0;
       for (int it = 0; it < my_tiles; ++it) {
         const int tile = blockIdx.x + it * gridDim.x;
@@ -243,13 +246,14 @@ conv2_dgrad_tc_kernel(const __grid_constant__ CUtensorMap mapDY, const __grid_co
           const int tap = kb >> 1, kc = kb & 1, kh = tap / 3, kw = tap - kh * 3;
           const int s = g % D_STAGES;
           mbar_wait(&empty_bar[s], ((g / D_STAGES) & 1) ^ 1);
-          mbar_expect_tx(&full_bar[s], D_A_BYTES);
-          tma_load_4d(asm_ + s * D_A_STRIDE, &mapDY, &full_bar[s], kc * 32, -kw, y0 - kh, pair * 2);
+          if (leader) mbar_expect_tx(&full_bar[s], D_A_BYTES);
+          if (leader) tma_load_4d(asm_ + s * D_A_STRIDE, &mapDY, &full_bar[s], kc * 32, -kw, y0 - kh, pair * 2);
         }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    {
+      const bool leader = elect_one();  // whole warp stays convergent: operands live in uniform registers
       constexpr uint32_t idesc = idesc_tf32(128, 32, 0, 1);
       mbar_wait(&w_bar, 0);
       int g = 0;
@@ -267,10 +271,10 @@ conv2_dgrad_tc_kernel(const __grid_constant__ CUtensorMap mapDY, const __grid_co
           const uint32_t sw = smem_u32(wsm + tap * TAP_BYTES + kc * 4096);
 #pragma unroll
           for (int kk = 0; kk < 4; ++kk)
-            umma_tf32(d, desc_kmajor(sa + kk * 32), desc_mnmajor(sw + kk * 1024, TAP_BYTES), idesc, (kb | kk) != 0);
-          umma_commit(&empty_bar[s]);
+            if (leader) umma_tf32(d, desc_kmajor(sa + kk * 32), desc_mnmajor(sw + kk * 1024, TAP_BYTES), idesc, (kb | kk) != 0);
+          if (leader) umma_commit(&empty_bar[s]);
         }
-        umma_commit(&tfull_bar[acc]);
+        if (leader) umma_commit(&tfull_bar[acc]);
       }
     }
   } else {
@@ -345,22 +349,24 @@ conv2_wgrad_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_co
   const int my_blocks = (nkblk - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
 
   if (warp == 0) {
-    if (lane == 0) {
+    {
+      const bool leader = elect_one();  // whole warp stays convergent: operands live in uniform registers
       for (int it = 0; it < my_blocks; ++it) {
         const int kblk = blockIdx.x + it * gridDim.x;
         const int n = kblk / 9, blk = kblk - n * 9, by = (blk / 3) * 8, bx = (blk % 3) * 8;
         const int s = it % G_STAGES;
         mbar_wait(&empty_bar[s], ((it / G_STAGES) & 1) ^ 1);
         uint8_t* st = smem + s * G_STAGE_BYTES;
-        mbar_expect_tx(&full_bar[s], G_LOAD_BYTES);
+        if (leader) mbar_expect_tx(&full_bar[s], G_LOAD_BYTES);
         for (int tap = 0; tap < 9; ++tap)
-          tma_load_4d(st + tap * TAP_BYTES, &mapA1, &full_bar[s], 0, bx + tap % 3, by + tap / 3, n);
-        tma_load_4d(st + 9 * TAP_BYTES, &mapDY, &full_bar[s], 0, bx, by, n);
-        tma_load_4d(st + 10 * TAP_BYTES, &mapDY, &full_bar[s], 32, bx, by, n);
+          if (leader) tma_load_4d(st + tap * TAP_BYTES, &mapA1, &full_bar[s], 0, bx + tap % 3, by + tap / 3, n);
+        if (leader) tma_load_4d(st + 9 * TAP_BYTES, &mapDY, &full_bar[s], 0, bx, by, n);
+        if (leader) tma_load_4d(st + 10 * TAP_BYTES, &mapDY, &full_bar[s], 32, bx, by, n);
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    {
+      const bool leader = elect_one();  // whole warp stays convergent: operands live in uniform registers
       constexpr uint32_t idesc = idesc_tf32(128, 64, 1, 1);
       for (int it = 0; it < my_blocks; ++it) {
         const int s = it % G_STAGES;
@@ -372,12 +378,12 @@ conv2_wgrad_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_co
           const uint64_t bd = desc_mnmajor(st + 9 * TAP_BYTES + kk * 1024, TAP_BYTES);
 #pragma unroll
           for (int grp = 0; grp < 3; ++grp)
-            umma_tf32(tmem_base + grp * 64, desc_mnmajor(st + grp * 4 * TAP_BYTES + kk * 1024, TAP_BYTES), bd, idesc,
+            if (leader) umma_tf32(tmem_base + grp * 64, desc_mnmajor(st + grp * 4 * TAP_BYTES + kk * 1024, TAP_BYTES), bd, idesc,
                       (it | kk) != 0);
         }
-        umma_commit(&empty_bar[s]);
+        if (leader) umma_commit(&empty_bar[s]);
       }
-      umma_commit(&tfull_bar);
+      if (leader) umma_commit(&tfull_bar);
     }
   } else {
     const int q = warp & 3;

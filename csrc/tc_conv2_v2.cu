@@ -27,7 +27,8 @@ namespace {
 
 constexpr int TAP_BYTES = 64 * 128;
 constexpr int P_ROWS = 18, P_PITCH = 32;
-constexpr int PATCH_BYTES = P_ROWS * P_PITCH * 128;  // 73,728
+constexpr int ROW_BYTES = P_PITCH * 128;             // one patch row = one TMA request (4 KiB)
+constexpr int PATCH_BYTES = P_ROWS * ROW_BYTES;      // 73,728
 constexpr int V2_SMEM = 9 * TAP_BYTES + 2 * PATCH_BYTES + 1024;
 
 // 2x2 max-pool over the (lane^1, lane^8) neighbourhood of a 128x64 accumulator tile held as
@@ -120,18 +121,21 @@ conv2_fwd_tc2_kernel(const __grid_constant__ CUtensorMap mapP, const __grid_cons
   const int my_items = (nitems - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
 
   if (warp == 0) {
-    if (lane == 0) {
-      mbar_expect_tx(&w_bar, 9 * TAP_BYTES);
-      for (int t = 0; t < 9; ++t) tma_load_2d(wsm + t * TAP_BYTES, &mapW, &w_bar, 0, t * 64);
+    {
+      const bool leader = elect_one();  // whole warp stays convergent: operands live in uniform registers
+      if (leader) mbar_expect_tx(&w_bar, 9 * TAP_BYTES);
+      for (int t = 0; t < 9; ++t) if (leader) tma_load_2d(wsm + t * TAP_BYTES, &mapW, &w_bar, 0, t * 64);
       for (int it = 0; it < my_items; ++it) {
         const int item = blockIdx.x + it * gridDim.x, n = item >> 1, y0 = (item & 1) * 8, buf = it & 1;
         mbar_wait(&pempty[buf], ((it >> 1) & 1) ^ 1);
-        mbar_expect_tx(&pfull[buf], PATCH_BYTES);
-        tma_load_4d(patch + buf * PATCH_BYTES, &mapP, &pfull[buf], 0, 0, y0, n);
+        if (leader) mbar_expect_tx(&pfull[buf], PATCH_BYTES);
+        for (int r = 0; r < P_ROWS; ++r)  // one request per patch row: many small TMA requests in flight
+          if (leader) tma_load_4d(patch + buf * PATCH_BYTES + r * ROW_BYTES, &mapP, &pfull[buf], 0, 0, y0 + r, n);
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    {
+      const bool leader = elect_one();  // whole warp stays convergent: operands live in uniform registers
       constexpr uint32_t idesc = idesc_tf32(128, 64, 0, 0);
       mbar_wait(&w_bar, 0);
       for (int it = 0; it < my_items; ++it) {
@@ -151,12 +155,12 @@ conv2_fwd_tc2_kernel(const __grid_constant__ CUtensorMap mapP, const __grid_cons
             const uint32_t sw = smem_u32(wsm + tap * TAP_BYTES);
 #pragma unroll
             for (int kk = 0; kk < 4; ++kk)
-              umma_tf32(d, desc_kmajor_view(sa + kk * 32, P_PITCH * 128), desc_kmajor(sw + kk * 32), idesc,
+              if (leader) umma_tf32(d, desc_kmajor_view(sa + kk * 32, P_PITCH * 128), desc_kmajor(sw + kk * 32), idesc,
                         (tap | kk) != 0);
           }
-          umma_commit(&tfull[slot]);
+          if (leader) umma_commit(&tfull[slot]);
         }
-        umma_commit(&pempty[buf]);  // every MMA reading this patch has completed
+        if (leader) umma_commit(&pempty[buf]);  // every MMA reading this patch has completed
       }
     }
   } else {
@@ -232,20 +236,23 @@ conv2_dgrad_tc2_kernel(const __grid_constant__ CUtensorMap mapDY, const __grid_c
   const int my_items = (nitems - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
 
   if (warp == 0) {
-    if (lane == 0) {
-      mbar_expect_tx(&w_bar, 9 * TAP_BYTES);
-      for (int t = 0; t < 9; ++t) tma_load_2d(wsm + t * TAP_BYTES, &mapW, &w_bar, 0, t * 64);
+    {
+      const bool leader = elect_one();  // whole warp stays convergent: operands live in uniform registers
+      if (leader) mbar_expect_tx(&w_bar, 9 * TAP_BYTES);
+      for (int t = 0; t < 9; ++t) if (leader) tma_load_2d(wsm + t * TAP_BYTES, &mapW, &w_bar, 0, t * 64);
       for (int it = 0; it < my_items; ++it) {
         const int item = blockIdx.x + it * gridDim.x, n = item >> 1, y0 = (item & 1) * 10;
         for (int kc = 0; kc < 2; ++kc) {  // stage == kc: chunk kc of every item goes through stage kc
           mbar_wait(&pempty[kc], (it & 1) ^ 1);
-          mbar_expect_tx(&pfull[kc], PATCH_BYTES);
-          tma_load_4d(patch + kc * PATCH_BYTES, &mapDY, &pfull[kc], kc * 32, -2, y0 - 2, n);
+          if (leader) mbar_expect_tx(&pfull[kc], PATCH_BYTES);
+          for (int r = 0; r < P_ROWS; ++r)
+            if (leader) tma_load_4d(patch + kc * PATCH_BYTES + r * ROW_BYTES, &mapDY, &pfull[kc], kc * 32, -2, y0 - 2 + r, n);
         }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    {
+      const bool leader = elect_one();  // whole warp stays convergent: operands live in uniform registers
       constexpr uint32_t idesc = idesc_tf32(128, 32, 0, 1);
       mbar_wait(&w_bar, 0);
       for (int it = 0; it < my_items; ++it) {
@@ -268,12 +275,12 @@ conv2_dgrad_tc2_kernel(const __grid_constant__ CUtensorMap mapDY, const __grid_c
               const uint32_t sw = smem_u32(wsm + tap * TAP_BYTES + kc * 4096);
 #pragma unroll
               for (int kk = 0; kk < 4; ++kk)
-                umma_tf32(d, desc_kmajor_view(sa + kk * 32, P_PITCH * 128), desc_mnmajor(sw + kk * 1024, TAP_BYTES),
+                if (leader) umma_tf32(d, desc_kmajor_view(sa + kk * 32, P_PITCH * 128), desc_mnmajor(sw + kk * 1024, TAP_BYTES),
                           idesc, (kc | tap | kk) != 0);
             }
-            if (kc == 1) umma_commit(&tfull[slot]);
+            if (kc == 1) if (leader) umma_commit(&tfull[slot]);
           }
-          umma_commit(&pempty[kc]);
+          if (leader) umma_commit(&pempty[kc]);
         }
       }
     }
@@ -350,19 +357,23 @@ conv2_wgrad_tc2_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_c
   const int my_items = (nitems - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
 
   if (warp == 0) {
-    if (lane == 0) {
+    {
+      const bool leader = elect_one();  // whole warp stays convergent: operands live in uniform registers
       for (int it = 0; it < my_items; ++it) {
         const int item = blockIdx.x + it * gridDim.x, n = item / 3, y0 = (item - n * 3) * 8, s = it & 1;
         mbar_wait(&empty_bar[s], ((it >> 1) & 1) ^ 1);
         uint8_t* st = smem + s * WG_STAGE;
-        mbar_expect_tx(&full_bar[s], WG_STAGE);
-        tma_load_4d(st, &mapA1, &full_bar[s], 0, 0, y0, n);
-        tma_load_4d(st + WG_A_BYTES, &mapDY, &full_bar[s], 0, 0, y0, n);
-        tma_load_4d(st + WG_A_BYTES + WG_Y_BYTES, &mapDY, &full_bar[s], 32, 0, y0, n);
+        if (leader) mbar_expect_tx(&full_bar[s], WG_STAGE);
+        for (int r = 0; r < 10; ++r) if (leader) tma_load_4d(st + r * ROW_BYTES, &mapA1, &full_bar[s], 0, 0, y0 + r, n);
+        for (int r = 0; r < 8; ++r) {
+          if (leader) tma_load_4d(st + WG_A_BYTES + r * ROW_BYTES, &mapDY, &full_bar[s], 0, 0, y0 + r, n);
+          if (leader) tma_load_4d(st + WG_A_BYTES + WG_Y_BYTES + r * ROW_BYTES, &mapDY, &full_bar[s], 32, 0, y0 + r, n);
+        }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    {
+      const bool leader = elect_one();  // whole warp stays convergent: operands live in uniform registers
       constexpr uint32_t idesc = idesc_tf32(128, 64, 1, 1);
       for (int it = 0; it < my_items; ++it) {
         const int s = it & 1;
@@ -375,13 +386,13 @@ conv2_wgrad_tc2_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_c
           const uint64_t bd = desc_mnmajor_view(sy + (uint32_t)((yy * P_PITCH + x0) * 128), WG_Y_BYTES, 512);
 #pragma unroll
           for (int kh = 0; kh < 3; ++kh)
-            umma_tf32(tmem_base + kh * 64,
+            if (leader) umma_tf32(tmem_base + kh * 64,
                       desc_mnmajor_view(sa + (uint32_t)(((yy + kh) * P_PITCH + x0) * 128), 128, 512), bd, idesc,
                       (it | ks) != 0);
         }
-        umma_commit(&empty_bar[s]);
+        if (leader) umma_commit(&empty_bar[s]);
       }
-      umma_commit(&tfull_bar);
+      if (leader) umma_commit(&tfull_bar);
     }
   } else {
     const int q = warp & 3;  // = kw of the rows this warp reads (q == 3: don't-care chunk)
@@ -428,11 +439,11 @@ int get_map(const float* p, int batch, int kind, CUtensorMap* out) {
     r = tcmap::encode(&m, p, 2, dims, strides, box, kind == 3);
   } else if (kind == 0 || kind == 4) {  // 32 px pitch: columns >= 26 are zero-filled
     uint64_t dims[4] = {32, 26, 26, (uint64_t)batch}, strides[3] = {128, 26 * 128, 676 * 128};
-    uint32_t box[4] = {32, P_PITCH, (uint32_t)(kind == 0 ? P_ROWS : 10), 1};
+    uint32_t box[4] = {32, P_PITCH, 1, 1};  // one patch row per request
     r = tcmap::encode(&m, p, 4, dims, strides, box, kind == 4);
   } else {
     uint64_t dims[4] = {64, 24, 24, (uint64_t)batch}, strides[3] = {256, 24 * 256, 576 * 256};
-    uint32_t box[4] = {32, P_PITCH, (uint32_t)(kind == 2 ? P_ROWS : 8), 1};
+    uint32_t box[4] = {32, P_PITCH, 1, 1};
     r = tcmap::encode(&m, p, 4, dims, strides, box, kind == 5);
   }
   if (r != B200_OK) return r;

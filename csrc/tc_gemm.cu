@@ -95,22 +95,26 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
   const uint32_t tmem_base = tmem_base_smem;
 
   if (warp == 0) {
-    if (lane == 0) {
+    {
+      const bool leader = elect_one();  // whole warp stays convergent: operands live in uniform registers
       for (int kb = 0; kb < nkb; ++kb) {
         const int s = kb % STAGES;
         mbar_wait(&empty_bar[s], ((kb / STAGES) & 1) ^ 1);
         uint8_t* sa = smem + s * STAGE_BYTES;
         uint8_t* sb = sa + A_BYTES;
-        mbar_expect_tx(&full_bar[s], STAGE_BYTES);
+        if (leader) mbar_expect_tx(&full_bar[s], STAGE_BYTES);
         const int k0 = (kb0 + kb) * BK;
-        if (A_MN) tma_load_3d(sa, &mapA, &full_bar[s], 0, k0, m0 / 32);
-        else tma_load_2d(sa, &mapA, &full_bar[s], k0, m0);
-        if (B_MN) tma_load_3d(sb, &mapB, &full_bar[s], 0, k0, n0 / 32);
-        else tma_load_2d(sb, &mapB, &full_bar[s], k0, n0);
+        if (leader) {
+          if (A_MN) tma_load_3d(sa, &mapA, &full_bar[s], 0, k0, m0 / 32);
+          else tma_load_2d(sa, &mapA, &full_bar[s], k0, m0);
+          if (B_MN) tma_load_3d(sb, &mapB, &full_bar[s], 0, k0, n0 / 32);
+          else tma_load_2d(sb, &mapB, &full_bar[s], k0, n0);
+        }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    {
+      const bool leader = elect_one();  // whole warp stays convergent: operands live in uniform registers
       constexpr uint32_t idesc = idesc_tf32(BM, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
       for (int kb = 0; kb < nkb; ++kb) {
         const int s = kb % STAGES;
@@ -121,11 +125,11 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
         for (int kk = 0; kk < BK / 8; ++kk) {
           const uint64_t ad = A_MN ? desc_mnmajor(sa + kk * 1024, BK * 128) : desc_kmajor(sa + kk * 32);
           const uint64_t bd = B_MN ? desc_mnmajor(sb + kk * 1024, BK * 128) : desc_kmajor(sb + kk * 32);
-          umma_tf32(tmem_base, ad, bd, idesc, (kb | kk) != 0);
+          if (leader) umma_tf32(tmem_base, ad, bd, idesc, (kb | kk) != 0);
         }
-        umma_commit(&empty_bar[s]);  // frees the smem slot once these MMAs have read it
+        if (leader) umma_commit(&empty_bar[s]);  // frees the smem slot once these MMAs have read it
       }
-      umma_commit(&tmem_full_bar);
+      if (leader) umma_commit(&tmem_full_bar);
     }
   } else {
     const int q = warp & 3;  // TMEM sub-partition this warp may read
