@@ -22,6 +22,7 @@
 // [b][r] of every peer with st.release.sys and spins with ld.acquire.sys on its own slots.  Spins are
 // bounded and trap.  The kernels also run all ranks inside ONE cooperative launch (blockIdx.y = rank)
 // so that they can be tested on a single GPU.
+#include <cstdlib>
 #include <vector>
 
 #include "common.cuh"
@@ -59,9 +60,11 @@ __device__ __forceinline__ void st_peer_f4(float* p, float4 v) {
   asm volatile("st.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
 }
 
-// phase 0 = "my gradients are complete", phase 1 = "I have finished reading / my writes are out"
+// phase 0 = "my gradients are complete", phase 1 = "I have finished reading / my writes are out".
+// No explicit fence is needed before the signal: gradients were written by EARLIER kernels (a kernel
+// boundary makes them visible system-wide), and the st.release.sys that follows the CTA barrier is
+// cumulative over everything the CTA's threads wrote before that barrier (two-shot parameter stores).
 __device__ __forceinline__ void comm_barrier(const CommArgs& a, int phase, uint32_t tok) {
-  __threadfence_system();
   __syncthreads();
   if ((int)threadIdx.x < a.world) {
     const int idx = ((a.channel * 2 + phase) * SYMM_MAX_BLOCKS + blockIdx.x) * SYMM_MAX_WORLD;
@@ -75,9 +78,11 @@ __device__ __forceinline__ void comm_barrier(const CommArgs& a, int phase, uint3
   __syncthreads();
 }
 
+// advance > -1: the last CTA to finish also advances the control block (end-of-step marker)
 template <int MODE, bool OPT>
 __global__ void __launch_bounds__(512)
-fused_allreduce_kernel(const CommArgs* __restrict__ table, uint32_t token, float rho, float eps) {
+fused_allreduce_kernel(const CommArgs* __restrict__ table, uint32_t token, float rho, float eps, int advance,
+                       unsigned int* __restrict__ done_counter) {
   const CommArgs& a = table[blockIdx.y];
   const int W = a.world, r = a.rank;
   const uint32_t tok = token ? token : (uint32_t)(a.ctrl->step) * 2u + 1u;
@@ -101,7 +106,7 @@ fused_allreduce_kernel(const CommArgs* __restrict__ table, uint32_t token, float
     float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
     for (int q = 0; q < SYMM_MAX_WORLD; ++q) {
-      if (q < W) {
+      if (q < W) {  // fixed rank order on every rank: bit-identical sums
         const float4 g = ld_peer_f4(gp[q] + 4 * (size_t)i);
         s.x += g.x; s.y += g.y; s.z += g.z; s.w += g.w;
       }
@@ -129,6 +134,15 @@ fused_allreduce_kernel(const CommArgs* __restrict__ table, uint32_t token, float
     }
   }
   comm_barrier(a, 1, tok + 1u);
+  if (advance >= 0 && threadIdx.x == 0) {
+    __threadfence();
+    if (atomicAdd(done_counter, 1u) == gridDim.x - 1) {  // every CTA has read ctrl->step / lr by now
+      *done_counter = 0;
+      B200Ctrl* c = const_cast<B200Ctrl*>(a.ctrl);
+      c->step += 1;
+      c->pos += advance;
+    }
+  }
 }
 
 struct CommPlan {
@@ -181,13 +195,14 @@ int default_blocks(const CommPlan* p, int mode) {
   return min(min(nb, cap), SYMM_MAX_BLOCKS);
 }
 
-int run_plan(const CommPlan* p, int mode, int opt, uint32_t token, int nblocks, float rho, float eps, cudaStream_t s) {
+int run_plan(const CommPlan* p, int mode, int opt, uint32_t token, int nblocks, float rho, float eps, cudaStream_t s,
+             int advance = -1, unsigned int* done_counter = nullptr) {
   B200_REQUIRE(p && (mode == 0 || mode == 1), "comm run: bad plan/mode");
   if (nblocks <= 0) nblocks = default_blocks(p, mode);
   B200_REQUIRE(nblocks <= SYMM_MAX_BLOCKS, "comm run: at most %d CTAs", SYMM_MAX_BLOCKS);
   dim3 grid(nblocks, p->slots);
   const CommArgs* tab = p->dev;
-  void* args[] = {(void*)&tab, (void*)&token, (void*)&rho, (void*)&eps};
+  void* args[] = {(void*)&tab, (void*)&token, (void*)&rho, (void*)&eps, (void*)&advance, (void*)&done_counter};
   const void* fn = mode == 0 ? (opt ? (const void*)fused_allreduce_kernel<0, true> : (const void*)fused_allreduce_kernel<0, false>)
                              : (opt ? (const void*)fused_allreduce_kernel<1, true> : (const void*)fused_allreduce_kernel<1, false>);
   if (p->slots > 1) {
@@ -208,13 +223,10 @@ struct DdpState {
   cudaEvent_t fork = nullptr, join = nullptr;
 };
 
-__global__ void ctrl_advance_kernel(B200Ctrl* c, int advance) {
-  c->step += 1;
-  c->pos += advance;
-}
-
 int hook_bucket_ready(Engine* E, int bucket, cudaStream_t s) {
   DdpState* d = (DdpState*)E->hooks.state;
+  static const bool no_side = getenv("B200_DDP_NO_SIDE") != nullptr;  // diagnostics: serialise bucket 0
+  if (bucket == 0 && no_side) return run_plan(d->plan[0], d->mode[0], 1, 0, 0, 0.9f, 1e-6f, s);
   if (bucket == 0) {
     // fc buckets are complete while the conv backward still runs: reduce them on a side stream
     B200_CHECK(cudaEventRecord(d->fork, s));
@@ -224,16 +236,16 @@ int hook_bucket_ready(Engine* E, int bucket, cudaStream_t s) {
     B200_CHECK(cudaEventRecord(d->join, d->comm));
     return B200_OK;
   }
-  return run_plan(d->plan[1], d->mode[1], 1, 0, 0, 0.9f, 1e-6f, s);
+  return B200_OK;  // bucket 1 is launched by hook_step_end (it also advances the control block)
 }
 
 int hook_step_end(Engine* E, int advance, cudaStream_t s) {
   DdpState* d = (DdpState*)E->hooks.state;
-  B200_CHECK(cudaStreamWaitEvent(s, d->join, 0));
-  ctrl_advance_kernel<<<1, 1, 0, s>>>(E->ctrl, advance);
-  b200_count_launch();
-  B200_LAUNCH_CHECK();
-  return B200_OK;
+  static const bool no_side = getenv("B200_DDP_NO_SIDE") != nullptr;
+  // The conv bucket's kernel is the last one of the step: it waits for the side stream (bucket 0
+  // reads ctrl->step and lr, which this kernel's last CTA advances) and then ends the step.
+  if (!no_side) B200_CHECK(cudaStreamWaitEvent(s, d->join, 0));
+  return run_plan(d->plan[1], d->mode[1], 1, 0, 0, 0.9f, 1e-6f, s, advance, E->done_counter);
 }
 
 void hook_destroy(Engine* E) {

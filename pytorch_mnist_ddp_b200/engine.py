@@ -209,7 +209,8 @@ class B200Backend:
         model = Net()  # CPU construction right after manual_seed: reference init stream
         self.ddp = None
         external = None
-        if info.distributed and world > 1:
+        # B200_FORCE_DDP=1 runs the data-parallel code path even with one rank (overhead measurements)
+        if (info.distributed and world > 1) or os.environ.get("B200_FORCE_DDP") == "1":
             from .parallel.fused_ddp import FusedDataParallel
             self.ddp = FusedDataParallel(info, comm=comm)
             external = self.ddp.allocate(ParamLayout().total)
@@ -235,9 +236,7 @@ class B200Backend:
 
     def train_step(self, step: int, batch: int, want_loss: bool = True):
         bsz = min(batch, self._epoch_n - step * batch)
-        s = self.engine.train_step(bsz, self.use_graph)
-        if self._nccl_baseline:
-            self._nccl_reduce_and_update(bsz)
+        s = self.step(bsz)
         if not want_loss:
             return None
         slot = self._slot
@@ -248,6 +247,13 @@ class B200Backend:
             ev = torch.cuda.Event()
             ev.record()
         return (slot, ev)
+
+    def step(self, bsz: int) -> int:
+        """One full optimizer step on the next `bsz` samples of the epoch (whatever the comm mode)."""
+        s = self.engine.train_step(bsz, self.use_graph)
+        if self._nccl_baseline:
+            self._nccl_reduce_and_update(bsz)
+        return s
 
     def _nccl_reduce_and_update(self, bsz: int) -> None:
         """Reference-style reduction (mnist_ddp.py:173 via ncclAllReduce per bucket), then Adadelta."""

@@ -161,14 +161,15 @@ class FusedDataParallel:
     def attach(self, engine) -> None:
         lib = N.lib()
         # DDP's _sync_module_states: every rank takes rank 0's parameters, pulled over NVLink
+        barrier = dist.barrier if dist.is_initialized() else (lambda: None)
         engine.synchronize()
-        dist.barrier()
+        barrier()
         N.check(lib.b200_symm_pull(self.arena.handle, 0, 0, self.total, engine._s()))
         engine.synchronize()
-        dist.barrier()
+        barrier()
         if self.comm != "nccl":
             N.check(lib.b200_ddp_attach(engine.handle, self.arena.handle, self.modes[0], self.modes[1]))
-        dist.barrier()
+        barrier()
 
     def verify_replicas(self) -> float:
         """max |p_rank - p_rank0| over all parameters (should be exactly 0: fixed reduction order)."""
