@@ -79,8 +79,10 @@ __device__ __forceinline__ void comm_barrier(const CommArgs& a, int phase, uint3
 }
 
 // advance > -1: the last CTA to finish also advances the control block (end-of-step marker)
+// <= 64 registers/thread on purpose: this kernel runs on a side stream NEXT TO the persistent conv
+// backward kernels and must not crowd their CTAs out of the register file.
 template <int MODE, bool OPT>
-__global__ void __launch_bounds__(512)
+__global__ void __launch_bounds__(512, 2)
 fused_allreduce_kernel(const CommArgs* __restrict__ table, uint32_t token, float rho, float eps, int advance,
                        unsigned int* __restrict__ done_counter) {
   const CommArgs& a = table[blockIdx.y];
@@ -137,6 +139,77 @@ fused_allreduce_kernel(const CommArgs* __restrict__ table, uint32_t token, float
   if (advance >= 0 && threadIdx.x == 0) {
     __threadfence();
     if (atomicAdd(done_counter, 1u) == gridDim.x - 1) {  // every CTA has read ctrl->step / lr by now
+      *done_counter = 0;
+      B200Ctrl* c = const_cast<B200Ctrl*>(a.ctrl);
+      c->step += 1;
+      c->pos += advance;
+    }
+  }
+}
+
+// The conv bucket's last kernel: (1) reduce the per-CTA partial sums that the wgrad kernels left behind
+// into this rank's gradient bucket, (2) one-shot all-reduce across ranks, (3) 1/W + Adadelta, (4) end
+// of step.  One CTA owns 256 consecutive floats of the bucket from start to finish, so the only
+// cross-CTA ordering needed is the per-CTA cross-GPU barrier.  512 threads = 64 float4 columns x 8
+// partial slices (fixed combination order: deterministic).
+__global__ void __launch_bounds__(512)
+finalize_bucket_kernel(const CommArgs* __restrict__ table, FinalizeSegs segs, float rho, float eps, int advance,
+                       unsigned int* __restrict__ done_counter) {
+  __shared__ float4 red[8][64];
+  const CommArgs& a = table[0];
+  const int W = a.world, r = a.rank;
+  const uint32_t tok = (uint32_t)(a.ctrl->step) * 2u + 1u;
+  const float lr = a.ctrl->lr;
+  const int col = threadIdx.x & 63, slice = threadIdx.x >> 6;
+  const int off = blockIdx.x * 256;
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const FinalizeSegs::Seg sg = segs.seg[k];
+    const int e = off - sg.dst_off + 4 * col;
+    if (sg.src && e >= 0 && e < sg.n) {
+      for (int p = slice; p < sg.nparts; p += 8) {
+        const float4 v = *reinterpret_cast<const float4*>(sg.src + (size_t)p * sg.stride + e);
+        acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+      }
+    }
+  }
+  red[slice][col] = acc;
+  __syncthreads();
+  float* mygrad = const_cast<float*>(a.grad[r]) + off + 4 * col;
+  if (slice == 0) {
+    float4 t = red[0][col];
+#pragma unroll
+    for (int q = 1; q < 8; ++q) { const float4 v = red[q][col]; t.x += v.x; t.y += v.y; t.z += v.z; t.w += v.w; }
+    *reinterpret_cast<float4*>(mygrad) = t;
+  }
+  comm_barrier(a, 0, tok);  // release is cumulative over the gradient stores above
+  if (slice == 0) {
+    const size_t i4 = (size_t)off + 4 * col;
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+    for (int q = 0; q < SYMM_MAX_WORLD; ++q) {
+      if (q < W) {
+        const float4 g = ld_peer_f4(a.grad[q] + i4);
+        s.x += g.x; s.y += g.y; s.z += g.z; s.w += g.w;
+      }
+    }
+    s.x *= a.inv_world; s.y *= a.inv_world; s.z *= a.inv_world; s.w *= a.inv_world;
+    float4 p = *reinterpret_cast<const float4*>(a.param[r] + i4);
+    float4 vv = *reinterpret_cast<const float4*>(a.v + i4);
+    float4 uu = *reinterpret_cast<const float4*>(a.u + i4);
+    adadelta_update(s.x, p.x, vv.x, uu.x, lr, rho, eps);
+    adadelta_update(s.y, p.y, vv.y, uu.y, lr, rho, eps);
+    adadelta_update(s.z, p.z, vv.z, uu.z, lr, rho, eps);
+    adadelta_update(s.w, p.w, vv.w, uu.w, lr, rho, eps);
+    *reinterpret_cast<float4*>(a.v + i4) = vv;
+    *reinterpret_cast<float4*>(a.u + i4) = uu;
+    *reinterpret_cast<float4*>(a.param[r] + i4) = p;
+  }
+  comm_barrier(a, 1, tok + 1u);
+  if (advance >= 0 && threadIdx.x == 0) {
+    __threadfence();
+    if (atomicAdd(done_counter, 1u) == gridDim.x - 1) {
       *done_counter = 0;
       B200Ctrl* c = const_cast<B200Ctrl*>(a.ctrl);
       c->step += 1;
@@ -245,6 +318,14 @@ int hook_step_end(Engine* E, int advance, cudaStream_t s) {
   // The conv bucket's kernel is the last one of the step: it waits for the side stream (bucket 0
   // reads ctrl->step and lr, which this kernel's last CTA advances) and then ends the step.
   if (!no_side) B200_CHECK(cudaStreamWaitEvent(s, d->join, 0));
+  if (E->fin_valid) {
+    const int chunks = d->plan[1]->n4 / 64;  // the flat layout pads every segment to 256 floats
+    B200_REQUIRE(d->plan[1]->n4 % 64 == 0 && chunks <= SYMM_MAX_BLOCKS, "finalize: bucket 1 has %d float4", d->plan[1]->n4);
+    finalize_bucket_kernel<<<chunks, 512, 0, s>>>(d->plan[1]->dev, E->fin, 0.9f, 1e-6f, advance, E->done_counter);
+    b200_count_launch();
+    B200_LAUNCH_CHECK();
+    return B200_OK;
+  }
   return run_plan(d->plan[1], d->mode[1], 1, 0, 0, 0.9f, 1e-6f, s, advance, E->done_counter);
 }
 

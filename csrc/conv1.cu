@@ -164,8 +164,8 @@ extern "C" int b200_conv1_wgrad(const uint8_t* images, const int32_t* idx, const
   cudaStream_t s = (cudaStream_t)stream;
   conv1_wgrad_kernel<<<2 * batch, 256, 0, s>>>(images, idx, (const B200Ctrl*)ctrl, da1, part);
   b200_count_launch();
-  b200_launch_reduce_partials(dw, part, 288, 2 * batch, CONV1_PART, s);
-  b200_launch_reduce_partials(db, part + 288, 32, 2 * batch, CONV1_PART, s);
+  if (dw) b200_launch_reduce_partials(dw, part, 288, 2 * batch, CONV1_PART, s);  // NULL: caller reduces the partials
+  if (db) b200_launch_reduce_partials(db, part + 288, 32, 2 * batch, CONV1_PART, s);
   B200_LAUNCH_CHECK();
   return B200_OK;
 }

@@ -304,17 +304,21 @@ extern "C" int b200_conv2_wgrad_simt(const float* dp, const uint8_t* amax, const
   const int grid = min(batch * 9, sm_count());
   conv2_wgrad_simt_kernel<<<grid, 256, 0, s>>>(dp, amax, a1, part, batch);
   b200_count_launch();
-  b200_launch_reduce_partials(dw, part, W2_ELEMS, grid, CONV2_PART, s);
-  b200_launch_reduce_partials(db, part + W2_ELEMS, C2, grid, CONV2_PART, s);
+  if (dw) b200_launch_reduce_partials(dw, part, W2_ELEMS, grid, CONV2_PART, s);
+  if (db) b200_launch_reduce_partials(db, part + W2_ELEMS, C2, grid, CONV2_PART, s);
   B200_LAUNCH_CHECK();
   return B200_OK;
 }
 
 // db_part: scratch of b200_unpool_parts() * 64 floats and db [64], or both NULL to skip the bias gradient
 extern "C" int b200_unpool_parts(void) { return 2 * sm_count(); }
+extern "C" int b200_unpool_nparts(int batch) {  // partial rows actually written for this batch
+  const size_t n4 = (size_t)batch * HP * WP * (C2 / 4);
+  return (int)min((size_t)(2 * sm_count()), (n4 + 255) / 256);
+}
 extern "C" int b200_unpool_dense(const float* dp, const uint8_t* amax, float* dy, float* db_part, float* db, int batch,
                                  void* stream) {
-  B200_REQUIRE((db_part == nullptr) == (db == nullptr), "unpool_dense: db_part and db go together");
+  B200_REQUIRE(db == nullptr || db_part != nullptr, "unpool_dense: db needs the db_part scratch");
   const size_t n4 = (size_t)batch * HP * WP * (C2 / 4);
   const int grid = (int)min((size_t)(2 * sm_count()), (n4 + 255) / 256);
   cudaStream_t s = (cudaStream_t)stream;

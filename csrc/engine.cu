@@ -102,20 +102,37 @@ int enqueue_train(Engine* E, const uint8_t* images, const uint8_t* labels, const
   }
   // bucket 0 (fc1.*, fc2.*) is complete here
   if (E->hooks.bucket_ready) TRY(E->hooks.bucket_ready(E, 0, s));
+  // With data-parallel hooks the conv-bucket gradients are left as per-CTA partials: the step's last
+  // kernel reduces them, all-reduces, and applies Adadelta in one go (fin).
+  const bool fuse = E->hooks.bucket_ready != nullptr;
+  const long b1 = c.bucket_begin[1];
+  float* dw2 = fuse ? nullptr : G + c.offsets[2];
+  float* db2 = fuse ? nullptr : G + c.offsets[3];
+  int np2 = 0;
   if (E->use_tc & B200_TC_CONV2_BWD) {
-    TRY(b200_unpool_dense(E->dp, E->amax, E->dy, E->db_part, G + c.offsets[3], batch, s));
+    TRY(b200_unpool_dense(E->dp, E->amax, E->dy, E->db_part, db2, batch, s));
     if (E->use_tc & B200_TC_CONV2_V2) {
-      TRY(b200_conv2_wgrad_tc2(E->dy, E->a1, E->c2_part, G + c.offsets[2], batch, s));
+      TRY(b200_conv2_wgrad_tc2(E->dy, E->a1, E->c2_part, dw2, batch, s));
       TRY(b200_conv2_dgrad_tc2(E->dy, P + c.offsets[2], E->a1, E->da1, batch, s));
+      np2 = min(3 * batch, E->nsm);
     } else {
-      TRY(b200_conv2_wgrad_tc(E->dy, E->a1, E->c2_part, G + c.offsets[2], batch, s));
+      TRY(b200_conv2_wgrad_tc(E->dy, E->a1, E->c2_part, dw2, batch, s));
       TRY(b200_conv2_dgrad_tc(E->dy, P + c.offsets[2], E->a1, E->da1, batch, s));
+      np2 = min(9 * batch, E->nsm);
     }
+    E->fin.seg[1] = {E->db_part, b200_unpool_nparts(batch), C2, C2, (int)(c.offsets[3] - b1)};
   } else {
-    TRY(b200_conv2_wgrad_simt(E->dp, E->amax, E->a1, E->c2_part, G + c.offsets[2], G + c.offsets[3], batch, s));
+    TRY(b200_conv2_wgrad_simt(E->dp, E->amax, E->a1, E->c2_part, dw2, db2, batch, s));
     TRY(b200_conv2_dgrad_simt(E->dp, E->amax, P + c.offsets[2], E->a1, E->da1, batch, s));
+    np2 = min(9 * batch, E->nsm);
+    E->fin.seg[1] = {E->c2_part + 9 * C2 * C1, np2, 9 * C2 * C1 + C2, C2, (int)(c.offsets[3] - b1)};
   }
-  TRY(b200_conv1_wgrad(images, idx, E->ctrl, E->da1, E->c1_part, G + c.offsets[0], G + c.offsets[1], batch, s));
+  E->fin.seg[0] = {E->c2_part, np2, 9 * C2 * C1 + C2, 9 * C2 * C1, (int)(c.offsets[2] - b1)};
+  TRY(b200_conv1_wgrad(images, idx, E->ctrl, E->da1, E->c1_part, fuse ? nullptr : G + c.offsets[0],
+                       fuse ? nullptr : G + c.offsets[1], batch, s));
+  E->fin.seg[2] = {E->c1_part, 2 * batch, 320, 288, (int)(c.offsets[0] - b1)};
+  E->fin.seg[3] = {E->c1_part + 288, 2 * batch, 320, 32, (int)(c.offsets[1] - b1)};
+  E->fin_valid = fuse;
   if (E->hooks.bucket_ready) {
     TRY(E->hooks.bucket_ready(E, 1, s));
     TRY(E->hooks.step_end(E, advance, s));

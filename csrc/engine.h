@@ -8,6 +8,13 @@
 
 enum { B200_TC_CONV2_FWD = 1, B200_TC_FC1_FWD = 2, B200_TC_FC1_BWD = 4, B200_TC_CONV2_BWD = 8, B200_TC_CONV2_V2 = 16 };
 
+// Where the conv bucket's gradients still sit as per-CTA partial sums at the end of backward.  The
+// last kernel of the step (allreduce.cu: finalize_bucket_kernel) reduces them itself, so no separate
+// reduction kernels sit on the critical path.  dst_off: float offset inside the bucket (x256).
+struct FinalizeSegs {
+  struct Seg { const float* src; int nparts, stride, n, dst_off; } seg[4];
+};
+
 struct Engine;
 struct EngineHooks {
   // called (inside the step's stream order / graph capture) when a gradient bucket is complete
@@ -43,4 +50,6 @@ struct Engine {
   bool dropout = true;  // false: train without dropout (numerics / DDP-equivalence tests)
   std::set<std::pair<int, int>> warm_batches;  // (batch, mode) pairs that already ran eagerly once
   EngineHooks hooks;
+  FinalizeSegs fin{};       // filled by enqueue_train when fin_valid
+  bool fin_valid = false;
 };

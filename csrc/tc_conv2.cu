@@ -511,7 +511,7 @@ extern "C" int b200_conv2_wgrad_tc(const float* dy, const float* a1, float* part
   const int grid = min(nkblk, b200_sm_count());
   conv2_wgrad_tc_kernel<<<grid, 192, G_SMEM, s>>>(ma, md, part, nkblk);
   b200_count_launch();
-  b200_launch_reduce_partials(dw, part, W2_ELEMS, grid, CONV2_PART, s);
+  if (dw) b200_launch_reduce_partials(dw, part, W2_ELEMS, grid, CONV2_PART, s);
   B200_LAUNCH_CHECK();
   return B200_OK;
 }

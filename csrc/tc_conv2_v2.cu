@@ -515,7 +515,7 @@ extern "C" int b200_conv2_wgrad_tc2(const float* dy, const float* a1, float* par
   const int grid = min(nitems, b200_sm_count());
   conv2_wgrad_tc2_kernel<<<grid, 192, WG_SMEM, s>>>(ma, md, part, nitems);
   b200_count_launch();
-  b200_launch_reduce_partials(dw, part, 9 * C2 * C1, grid, CONV2_PART, s);
+  if (dw) b200_launch_reduce_partials(dw, part, 9 * C2 * C1, grid, CONV2_PART, s);
   B200_LAUNCH_CHECK();
   return B200_OK;
 }

@@ -63,6 +63,7 @@ int b200_conv2_wgrad_simt(const float* dp, const uint8_t* amax, const float* a1,
 /* dY[B][24][24][64] from the pooled gradient + argmax; optionally conv2's bias gradient db[64]
  * (db_part: scratch of b200_unpool_parts()*64 floats; pass both or neither) */
 int b200_unpool_parts(void);
+int b200_unpool_nparts(int batch);
 int b200_unpool_dense(const float* dp, const uint8_t* amax, float* dy, float* db_part, float* db, int batch,
                       void* stream);
 
