@@ -104,7 +104,7 @@ int enqueue_train(Engine* E, const uint8_t* images, const uint8_t* labels, const
   if (E->hooks.bucket_ready) TRY(E->hooks.bucket_ready(E, 0, s));
   // With data-parallel hooks the conv-bucket gradients are left as per-CTA partials: the step's last
   // kernel reduces them, all-reduces, and applies Adadelta in one go (fin).
-  const bool fuse = E->hooks.bucket_ready != nullptr;
+  const bool fuse = E->hooks.bucket_ready != nullptr || !E->defer_update;
   const long b1 = c.bucket_begin[1];
   float* dw2 = fuse ? nullptr : G + c.offsets[2];
   float* db2 = fuse ? nullptr : G + c.offsets[3];
@@ -137,7 +137,9 @@ int enqueue_train(Engine* E, const uint8_t* images, const uint8_t* labels, const
     TRY(E->hooks.bucket_ready(E, 1, s));
     TRY(E->hooks.step_end(E, advance, s));
   } else if (!E->defer_update) {
-    TRY(b200_adadelta(P, G, E->V, E->U, c.param_floats, E->ctrl, 0.9f, 1e-6f, advance, E->done_counter, s));
+    // bucket 0 occupies floats [0, bucket_begin[1]) of the flat layout, bucket 1 the rest
+    TRY(b200_adadelta_finalize(P, G, E->V, E->U, b1, (int)((c.bucket_end[1] - b1) / 256), E->fin, E->ctrl, 0.9f,
+                               1e-6f, advance, E->done_counter, s));
   }
   return B200_OK;
 }

@@ -15,6 +15,10 @@ struct FinalizeSegs {
   struct Seg { const float* src; int nparts, stride, n, dst_off; } seg[4];
 };
 
+// adadelta.cu: single-GPU end of step = partial reduction of the conv bucket + Adadelta on everything
+int b200_adadelta_finalize(float* p, float* g, float* v, float* u, long b1_off, int nchunks, const FinalizeSegs& segs,
+                           void* ctrl, float rho, float eps, int advance, unsigned int* done_counter, cudaStream_t s);
+
 struct Engine;
 struct EngineHooks {
   // called (inside the step's stream order / graph capture) when a gradient bucket is complete
