@@ -261,6 +261,10 @@ extern "C" int b200_engine_destroy(void* engine) {
     else ++it;
   }
   if (E->hooks.destroy) E->hooks.destroy(E);
+  if (E->copy_stream) {
+    cudaStreamDestroy(E->copy_stream);
+    for (int i = 0; i < 2; ++i) { cudaEventDestroy(E->ev_copied[i]); cudaEventDestroy(E->ev_consumed[i]); }
+  }
   for (void* p : E->owned) cudaFree(p);
   if (E->h_scratch) cudaFreeHost(E->h_scratch);
   delete E;
@@ -375,10 +379,25 @@ extern "C" int b200_engine_train_step_host(void* engine, const uint8_t* images_h
   const int par = (int)(E->steps & 1);
   uint8_t* di = E->stage_img + (size_t)par * E->cfg.max_batch * 784;
   uint8_t* dl = E->stage_lbl + (size_t)par * E->cfg.max_batch;
-  B200_CHECK(cudaMemcpyAsync(di, images_host, (size_t)batch * 784, cudaMemcpyHostToDevice, s));
-  B200_CHECK(cudaMemcpyAsync(dl, labels_host, (size_t)batch, cudaMemcpyHostToDevice, s));
+  // The copy runs on its own stream into one of two staging buffers, so the H2D transfer of step
+  // i+1 overlaps the compute of step i; events keep a buffer from being overwritten while a step
+  // still reads it.
+  if (!E->copy_stream) {
+    B200_CHECK(cudaStreamCreateWithFlags(&E->copy_stream, cudaStreamNonBlocking));
+    for (int i = 0; i < 2; ++i) {
+      B200_CHECK(cudaEventCreateWithFlags(&E->ev_copied[i], cudaEventDisableTiming));
+      B200_CHECK(cudaEventCreateWithFlags(&E->ev_consumed[i], cudaEventDisableTiming));
+    }
+  }
+  if (E->consumed_valid[par]) B200_CHECK(cudaStreamWaitEvent(E->copy_stream, E->ev_consumed[par], 0));
+  B200_CHECK(cudaMemcpyAsync(di, images_host, (size_t)batch * 784, cudaMemcpyHostToDevice, E->copy_stream));
+  B200_CHECK(cudaMemcpyAsync(dl, labels_host, (size_t)batch, cudaMemcpyHostToDevice, E->copy_stream));
+  B200_CHECK(cudaEventRecord(E->ev_copied[par], E->copy_stream));
+  B200_CHECK(cudaStreamWaitEvent(s, E->ev_copied[par], 0));
   // staged batches are addressed from sample 0: the cursor must not move (advance = 0)
   TRY(run_step(E, di, dl, nullptr, batch, 0, 2 + par, use_graph, s));
+  B200_CHECK(cudaEventRecord(E->ev_consumed[par], s));
+  E->consumed_valid[par] = true;
   E->steps++;
   return B200_OK;
 }

@@ -53,6 +53,9 @@ struct Engine {
   bool defer_update = false;  // true: train_step stops after backward (unfused NCCL baseline)
   bool dropout = true;  // false: train without dropout (numerics / DDP-equivalence tests)
   std::set<std::pair<int, int>> warm_batches;  // (batch, mode) pairs that already ran eagerly once
+  cudaStream_t copy_stream = nullptr;  // H2D staging for train_step_host (double buffered)
+  cudaEvent_t ev_copied[2] = {nullptr, nullptr}, ev_consumed[2] = {nullptr, nullptr};
+  bool consumed_valid[2] = {false, false};
   EngineHooks hooks;
   FinalizeSegs fin{};       // filled by enqueue_train when fin_valid
   bool fin_valid = false;
