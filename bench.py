@@ -183,14 +183,16 @@ def run_ours(args) -> dict:
     n_host = min(per_rank, (K + W) * B)
     host_img = train.images[idx[:n_host]].reshape(-1, 784).contiguous().pin_memory()
     host_lbl = train.labels[idx[:n_host]].contiguous().pin_memory()
-    host_loss = torch.zeros(K + W + 8, dtype=torch.float32).pin_memory()
     eng.begin_epoch(None)
     nb = n_host // B
 
+    steps_e2e = []
+
     def e2e_step(j, slot):
         o = (j % nb) * B
-        s = eng.train_step_host(host_img[o: o + B], host_lbl[o: o + B], use_graph=not args.no_graph)
-        host_loss[slot: slot + 1].copy_(eng.loss_ring[s % LOSS_RING: s % LOSS_RING + 1], non_blocking=True)
+        # H2D: this step's uint8 batch from pinned host memory (copy stream, overlaps the previous step);
+        # D2H: the step's head kernel stores its mean loss into mapped pinned host memory (4 bytes)
+        steps_e2e.append(backend.step_host(host_img[o: o + B], host_lbl[o: o + B]))
 
     for j in range(max(W, 4)):
         e2e_step(j, K + j % 8)
@@ -203,7 +205,8 @@ def run_ours(args) -> dict:
     barrier()
     e2e_ms = e0.elapsed_time(e1)
     clocks = sampler.stop()
-    losses_ok = bool(torch.isfinite(host_loss[:K]).all()) and float(host_loss[:K].abs().sum()) > 0
+    host_loss = torch.stack([eng.host_loss_ring[s % LOSS_RING] for s in steps_e2e[-min(K, LOSS_RING):]]).clone()
+    losses_ok = bool(torch.isfinite(host_loss).all()) and float(host_loss.abs().sum()) > 0
 
     def reduce_max(x):
         if world == 1:
@@ -232,13 +235,14 @@ def run_ours(args) -> dict:
                          "note": "same K steps back to back, no L2 flush"},
         "e2e": {"value": imgs / (e2e_ms / 1e3), "unit": "images/s", "ms_per_step": e2e_ms / K,
                 "h2d_bytes_per_step": B * 784 + B, "d2h_bytes_per_step": 4,
-                "api": "NativeEngine.train_step_host(pinned uint8 images, pinned uint8 labels) + loss D2H",
+                "api": "NativeEngine.train_step_host(pinned uint8 images, pinned uint8 labels); the loss of every "
+                       "step is stored by the head kernel into mapped pinned host memory (zero-copy D2H)",
                 "losses_finite": losses_ok},
         "gpu_launches": int(launches),
         "launches_per_step": eng.launches_per_step(B),
         "host_wall_s_timed_region": t_wall,
         "clocks": clocks,
-        "last_loss": float(host_loss[K - 1]),
+        "last_loss": float(host_loss[-1]),
     }
     if world > 1:
         dist.barrier()

@@ -16,6 +16,7 @@
 // allreduce.cu on a second stream (bucket 0 overlaps the conv backward) instead of the local
 // Adadelta.  Gradients are written straight into the flat (symmetric) bucket: there is no
 // bucket copy-in/copy-out and no zero_grad (every wgrad kernel overwrites).
+#include <cstring>
 #include <map>
 #include <utility>
 #include <vector>
@@ -89,7 +90,7 @@ int enqueue_train(Engine* E, const uint8_t* images, const uint8_t* labels, const
   const float drop1_scale = E->dropout ? 1.0f / (1.0f - P_DROP1) : 1.0f;
   TRY(enqueue_forward(E, images, labels, idx, E->ctrl, batch, true, s));
   TRY(b200_head_wgrad(E->h, E->dlogits, E->dh, E->loss_i, batch, G + c.offsets[6], G + c.offsets[7], G + c.offsets[5],
-                      E->loss_scalar, E->ctrl, E->loss_ring, B200_LOSS_RING, s));
+                      E->loss_scalar, E->ctrl, E->loss_ring, B200_LOSS_RING, E->loss_ring_host_dev, s));
   // fc1: dW1[128][9216] = dh^T . pooled ; dp = (dh . W1) * (pooled > 0 ? 1/(1-p1) : 0)
   if (E->use_tc & B200_TC_FC1_BWD) {
     TRY(b200_tc_gemm(E->dh, E->pooled, G + c.offsets[4], FC1_OUT, FC1_IN, batch, 1, 1, 1, 0, nullptr, 0.f, s));
@@ -244,6 +245,9 @@ extern "C" int b200_engine_create(const B200EngineConfig* cfg, void** out) {
 #undef A
   if (r != B200_OK) { b200_engine_destroy(E); return r; }
   B200_CHECK(cudaMallocHost((void**)&E->h_scratch, 64));
+  B200_CHECK(cudaHostAlloc((void**)&E->loss_ring_host, B200_LOSS_RING * sizeof(float), cudaHostAllocMapped));
+  memset(E->loss_ring_host, 0, B200_LOSS_RING * sizeof(float));
+  B200_CHECK(cudaHostGetDevicePointer((void**)&E->loss_ring_host_dev, E->loss_ring_host, 0));
   const float inv_w = 1.0f / (float)(cfg->world > 0 ? cfg->world : 1);
   TRY(b200_ctrl_set(E->ctrl, 0, cfg->seed, 0, 3, 1.0f, inv_w, nullptr));
   TRY(b200_ctrl_set(E->ctrl_eval, 0, cfg->seed, 0, 0, 0.0f, inv_w, nullptr));
@@ -267,6 +271,7 @@ extern "C" int b200_engine_destroy(void* engine) {
   }
   for (void* p : E->owned) cudaFree(p);
   if (E->h_scratch) cudaFreeHost(E->h_scratch);
+  if (E->loss_ring_host) cudaFreeHost(E->loss_ring_host);
   delete E;
   return B200_OK;
 }
@@ -443,6 +448,13 @@ extern "C" int b200_engine_read_loss(void* engine, unsigned long long step, floa
   B200_CHECK(cudaMemcpyAsync(hs, E->loss_ring + (step % B200_LOSS_RING), 4, cudaMemcpyDeviceToHost, s));
   B200_CHECK(cudaStreamSynchronize(s));
   *loss_host = *hs;
+  return B200_OK;
+}
+
+extern "C" int b200_engine_host_loss_ring(void* engine, float** ring_host) {
+  Engine* E = (Engine*)engine;
+  B200_REQUIRE(E && ring_host, "engine_host_loss_ring: null argument");
+  *ring_host = E->loss_ring_host;
   return B200_OK;
 }
 

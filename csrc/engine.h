@@ -49,6 +49,7 @@ struct Engine {
   unsigned int* done_counter = nullptr;
   double* eval_acc = nullptr;
   void* h_scratch = nullptr;  // 64 B pinned
+  float *loss_ring_host = nullptr, *loss_ring_host_dev = nullptr;  // mapped pinned ring + its device alias
   unsigned long long steps = 0;
   bool defer_update = false;  // true: train_step stops after backward (unfused NCCL baseline)
   bool dropout = true;  // false: train without dropout (numerics / DDP-equivalence tests)

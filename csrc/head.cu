@@ -122,7 +122,7 @@ __global__ void __launch_bounds__(1024)
 head_wgrad_kernel(const float* __restrict__ h, const float* __restrict__ dlogits, const float* __restrict__ dh,
                   const float* __restrict__ loss_i, int batch, float* __restrict__ dw2, float* __restrict__ db2,
                   float* __restrict__ db1, float* __restrict__ loss_out, const B200Ctrl* __restrict__ ctrl,
-                  float* __restrict__ loss_ring, int ring) {
+                  float* __restrict__ loss_ring, int ring, float* __restrict__ loss_ring_host) {
   __shared__ float red[8][FC1_OUT];
   const int j = threadIdx.x & 127, sl = threadIdx.x >> 7;
   const int per = (batch + 7) / 8, b0 = sl * per, b1 = min(batch, b0 + per);
@@ -149,6 +149,8 @@ head_wgrad_kernel(const float* __restrict__ h, const float* __restrict__ dlogits
       const float mean = t / (float)batch;
       loss_out[0] = mean;
       if (loss_ring) loss_ring[ctrl->step % (unsigned long long)ring] = mean;
+      // zero-copy result read-back: the same value goes straight into mapped, pinned HOST memory
+      if (loss_ring_host) loss_ring_host[ctrl->step % (unsigned long long)ring] = mean;
     }
   }
 }
@@ -185,10 +187,11 @@ extern "C" int b200_head_fused(const float* part, int splits, int batch, const f
 
 extern "C" int b200_head_wgrad(const float* h, const float* dlogits, const float* dh, const float* loss_i,
                                int batch, float* dw2, float* db2, float* db1, float* loss_out, const void* ctrl,
-                               float* loss_ring, int ring, void* stream) {
+                               float* loss_ring, int ring, float* loss_ring_host, void* stream) {
   B200_REQUIRE(batch > 0, "head_wgrad: bad batch");
   head_wgrad_kernel<<<NCLS + 2, 1024, 0, (cudaStream_t)stream>>>(h, dlogits, dh, loss_i, batch, dw2, db2, db1,
-                                                               loss_out, (const B200Ctrl*)ctrl, loss_ring, ring);
+                                                               loss_out, (const B200Ctrl*)ctrl, loss_ring, ring,
+                                                               loss_ring_host);
   b200_count_launch();
   B200_LAUNCH_CHECK();
   return B200_OK;

@@ -98,7 +98,7 @@ int b200_head_fused(const float* part, int splits, int batch, const float* b1, c
                     float* loss_i, int* correct_i, float* logp, void* stream);
 int b200_head_wgrad(const float* h, const float* dlogits, const float* dh, const float* loss_i, int batch, float* dw2,
                     float* db2, float* db1, float* loss_out, const void* ctrl, float* loss_ring, int ring,
-                    void* stream);
+                    float* loss_ring_host /* device alias of mapped pinned host memory, or NULL */, void* stream);
 int b200_eval_accumulate(const float* loss_i, const int* correct_i, int batch, double* acc, void* stream);
 
 /* ---- optimizer (mnist_ddp.py:73,176) ------------------------------------------------ */
@@ -155,6 +155,9 @@ int b200_engine_eval_result(void* engine, double* nll_sum_host, long long* corre
 /* mean loss of optimizer step `step` (must be among the last B200_LOSS_RING steps); syncs the stream */
 int b200_engine_read_loss(void* engine, unsigned long long step, float* loss_host, void* stream);
 int b200_engine_step_count(void* engine, unsigned long long* steps_host);
+/* host address of the mapped, pinned loss ring (B200_LOSS_RING floats): the head kernel writes every
+ * step's mean loss straight into it (zero-copy D2H); valid once the step's work has completed */
+int b200_engine_host_loss_ring(void* engine, float** ring_host);
 /* kernels launched per train step at this batch size (for bench.py's gpu_launches) */
 int b200_engine_launches_per_step(void* engine, int batch, int* n_host);
 

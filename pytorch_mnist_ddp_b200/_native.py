@@ -126,7 +126,8 @@ _SIGNATURES = {
     "b200_conv2_dgrad_tc": [_vp, _vp, _vp, _vp, _i, _vp],
     "b200_conv2_wgrad_tc": [_vp, _vp, _vp, _vp, _i, _vp],
     "b200_head_fused": [_vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp],
-    "b200_head_wgrad": [_vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp],
+    "b200_head_wgrad": [_vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp],
+    "b200_engine_host_loss_ring": [_vp, ctypes.POINTER(ctypes.POINTER(ctypes.c_float))],
     "b200_eval_accumulate": [_vp, _vp, _i, _vp, _vp],
     "b200_adadelta": [_vp, _vp, _vp, _vp, _l, _vp, _f, _f, _i, _vp, _vp],
     "b200_symm_create": [_i, _i, ctypes.c_size_t, ctypes.POINTER(_vp)],

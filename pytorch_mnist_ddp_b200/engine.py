@@ -86,6 +86,11 @@ class NativeEngine:
         self.sq_avg = self.buffer(BUF_SQ_AVG, torch.float32)
         self.acc_delta = self.buffer(BUF_ACC_DELTA, torch.float32)
         self.loss_ring = self.buffer(BUF_LOSS_RING, torch.float32)
+        ring = ctypes.POINTER(ctypes.c_float)()
+        N.check(self.lib.b200_engine_host_loss_ring(self.handle, ctypes.byref(ring)))
+        # mapped pinned host memory that the head kernel writes every step (zero-copy D2H)
+        self.host_loss_ring = torch.frombuffer((ctypes.c_float * LOSS_RING).from_address(
+            ctypes.addressof(ring.contents)), dtype=torch.float32)
         self.steps = 0
 
     # ---- plumbing
@@ -253,6 +258,13 @@ class B200Backend:
         s = self.engine.train_step(bsz, self.use_graph)
         if self._nccl_baseline:
             self._nccl_reduce_and_update(bsz)
+        return s
+
+    def step_host(self, images_u8: torch.Tensor, labels_u8: torch.Tensor) -> int:
+        """Same as `step`, but the batch is streamed from pinned host memory (uint8 images, uint8 labels)."""
+        s = self.engine.train_step_host(images_u8, labels_u8, self.use_graph)
+        if self._nccl_baseline:
+            self._nccl_reduce_and_update(0)
         return s
 
     def _nccl_reduce_and_update(self, bsz: int) -> None:

@@ -140,7 +140,7 @@ def head_wgrad(h, dlogits, dh, loss_i, ctrl):
     dw2, db2, db1 = torch.empty(10, 128, device="cuda"), torch.empty(10, device="cuda"), torch.empty(128, device="cuda")
     loss = torch.empty(4, device="cuda")
     N.check(N.lib().b200_head_wgrad(_p(h), _p(dlogits), _p(dh), _p(loss_i), batch, _p(dw2), _p(db2), _p(db1), _p(loss),
-                                    _p(ctrl), None, 0, _s()))
+                                    _p(ctrl), None, 0, None, _s()))
     return dw2, db2, db1, loss[0]
 
 
