@@ -54,7 +54,13 @@ def main():
         b *= 4
     sizes += list(BUCKETS.items())
     nmax = max(s for _, s in sizes) // 4
-    arena = SymmetricArena.create(info, 4 * nmax)  # [out/params | grads | v | u]
+    try:  # torch symmetric memory gives the NVLS multicast alias on top of the peer mapping
+        arena = SymmetricArena.create_torch(info, 4 * nmax)  # [out/params | grads | v | u]
+    except Exception as e:
+        if rank == 0:
+            print(f"# torch symmetric memory unavailable ({e!r}); falling back to the CUDA-IPC arena (no NVLS)")
+        arena = SymmetricArena.create(info, 4 * nmax)
+    has_mc = bool(getattr(arena, "has_multicast", False))
     view = arena.view()
     view[nmax:2 * nmax].normal_()
     ctrl = ops.make_ctrl(step=0, lr=1.0)
@@ -80,17 +86,25 @@ def main():
         n = nbytes // 4
         plan = CommPlan.create(arena, nmax, 0, 2 * nmax, 3 * nmax, n, channel=2, ctrl=ctrl)
         t_nccl = timed(lambda: dist.all_reduce(nccl_buf[:n]))
-        t_one = timed(lambda: plan.run(0, opt=False)) if nbytes * world <= (64 << 20) * 8 else None
-        t_two = timed(lambda: plan.run(1, opt=False))
+        # large messages get more CTAs than the 64 the training path uses (that cap keeps the reducer
+        # small enough to share SMs with the conv backward)
+        nb = max(1, min(256, nbytes // (64 << 10)))
+        t_one = timed(lambda: plan.run(0, opt=False, nblocks=nb)) if nbytes * world <= (64 << 20) * 8 else None
+        t_two = timed(lambda: plan.run(1, opt=False, nblocks=nb))
+        t_nvls = timed(lambda: plan.run(2, opt=False, nblocks=nb)) if has_mc else None
         bus = lambda t: None if t is None else 2 * (world - 1) / world * nbytes / t / 1e9
         row = {"size": name, "bytes": nbytes, "nccl_us": t_nccl * 1e6, "oneshot_us": None if t_one is None else t_one * 1e6,
-               "twoshot_us": t_two * 1e6, "nccl_busGBs": bus(t_nccl), "oneshot_busGBs": bus(t_one),
-               "twoshot_busGBs": bus(t_two)}
+               "twoshot_us": t_two * 1e6, "nvls_us": None if t_nvls is None else t_nvls * 1e6,
+               "nccl_busGBs": bus(t_nccl), "oneshot_busGBs": bus(t_one), "twoshot_busGBs": bus(t_two),
+               "nvls_busGBs": bus(t_nvls)}
         if name in BUCKETS:  # fused all-reduce + 1/W + Adadelta, with its roofline
-            for mode, key in ((0, "fused_oneshot"), (1, "fused_twoshot")):
+            for mode, key in ((0, "fused_oneshot"), (1, "fused_twoshot")) + (((2, "fused_nvls"),) if has_mc else ()):
                 t = timed(lambda: plan.run(mode, opt=True))  # explicit tokens, lr from ctrl
                 if mode == 0:
                     nvl, hbm = (world - 1) * nbytes, (world + 6) * nbytes      # read W grads; r/w p,v,u
+                elif mode == 2:  # per-GPU link traffic: its slice in (reduced by the switch) + its slice out
+                    nvl = 2 * nbytes / world
+                    hbm = 8 / world * nbytes + nbytes
                 else:
                     nvl = 2 * (world - 1) / world * nbytes                     # in: grads slices, out: params
                     hbm = (world + 6) / world * nbytes + (world - 1) / world * nbytes

@@ -35,6 +35,8 @@ struct CommArgs {
   const float* grad[SYMM_MAX_WORLD];  // start of the bucket in every rank's gradient buffer
   float* param[SYMM_MAX_WORLD];       // start of the bucket in every rank's parameter (or output) buffer
   uint32_t* flags[SYMM_MAX_WORLD];    // every rank's flag block
+  const float* mc_grad;               // NVLS multicast aliases of the same two buffers (or null)
+  float* mc_param;
   float* v;                           // local Adadelta state (bucket start); unused when OPT == false
   float* u;
   const B200Ctrl* ctrl;               // lr and step counter; may be null when token != 0 and OPT == false
@@ -55,6 +57,18 @@ __device__ __forceinline__ float4 ld_peer_f4(const float* p) {  // never served 
   asm volatile("ld.volatile.global.v4.f32 {%0,%1,%2,%3}, [%4];"
                : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p) : "memory");
   return r;
+}
+// NVLS: one load returns the SUM over all ranks' copies (reduced inside the NVSwitch); one store is
+// delivered to every rank's copy.
+__device__ __forceinline__ float4 multimem_ld_reduce_f4(const float* mc) {
+  float4 r;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(mc) : "memory");
+  return r;
+}
+__device__ __forceinline__ void multimem_st_f4(float* mc, float4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc), "f"(v.x), "f"(v.y), "f"(v.z),
+               "f"(v.w) : "memory");
 }
 __device__ __forceinline__ void st_peer_f4(float* p, float4 v) {
   asm volatile("st.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
@@ -98,7 +112,7 @@ fused_allreduce_kernel(const CommArgs* __restrict__ table, uint32_t token, float
   comm_barrier(a, 0, tok);
 
   int lo = 0, hi = a.n4;
-  if (MODE == 1) {
+  if (MODE >= 1) {
     const int per = (a.n4 + W - 1) / W;
     lo = min(a.n4, r * per);
     hi = min(a.n4, lo + per);
@@ -106,11 +120,15 @@ fused_allreduce_kernel(const CommArgs* __restrict__ table, uint32_t token, float
   const int stride = gridDim.x * blockDim.x;
   for (int i = lo + blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += stride) {
     float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (MODE == 2) {
+      s = multimem_ld_reduce_f4(a.mc_grad + 4 * (size_t)i);  // in-switch reduction (NVLS)
+    } else {
 #pragma unroll
-    for (int q = 0; q < SYMM_MAX_WORLD; ++q) {
-      if (q < W) {  // fixed rank order on every rank: bit-identical sums
-        const float4 g = ld_peer_f4(gp[q] + 4 * (size_t)i);
-        s.x += g.x; s.y += g.y; s.z += g.z; s.w += g.w;
+      for (int q = 0; q < SYMM_MAX_WORLD; ++q) {
+        if (q < W) {  // fixed rank order on every rank: bit-identical sums
+          const float4 g = ld_peer_f4(gp[q] + 4 * (size_t)i);
+          s.x += g.x; s.y += g.y; s.z += g.z; s.w += g.w;
+        }
       }
     }
     s.x *= inv_w; s.y *= inv_w; s.z *= inv_w; s.w *= inv_w;
@@ -129,12 +147,15 @@ fused_allreduce_kernel(const CommArgs* __restrict__ table, uint32_t token, float
     }
     if (MODE == 0) {
       *reinterpret_cast<float4*>(a.param[r] + 4 * (size_t)i) = out;
+    } else if (MODE == 2) {
+      multimem_st_f4(a.mc_param + 4 * (size_t)i, out);  // one store, delivered to every rank
     } else {
 #pragma unroll
       for (int q = 0; q < SYMM_MAX_WORLD; ++q)
         if (q < W) st_peer_f4(pp[q] + 4 * (size_t)i, out);
     }
   }
+  if (MODE == 2) __threadfence_system();  // multimem stores must be performed before the exit signal
   comm_barrier(a, 1, tok + 1u);
   if (advance >= 0 && threadIdx.x == 0) {
     __threadfence();
@@ -222,6 +243,7 @@ struct CommPlan {
   CommArgs* dev = nullptr;  // world_slots entries (1, or W when emulated)
   int slots = 1;
   int n4 = 0, world = 1;
+  bool has_mc = false;
 };
 
 int plan_from_arenas(SymmArena* const* arenas, int slots, size_t grad_off, size_t param_off, size_t v_off,
@@ -241,6 +263,8 @@ int plan_from_arenas(SymmArena* const* arenas, int slots, size_t grad_off, size_
       c.param[q] = (float*)a->peer[q] + param_off;
       c.flags[q] = a->flags(q);
     }
+    c.mc_grad = a->mc ? (const float*)a->mc + grad_off : nullptr;
+    c.mc_param = a->mc ? (float*)a->mc + param_off : nullptr;
     c.v = (float*)a->peer[a->rank] + v_off;
     c.u = (float*)a->peer[a->rank] + u_off;
     c.ctrl = ctrls ? ctrls[sidx] : nullptr;
@@ -254,6 +278,7 @@ int plan_from_arenas(SymmArena* const* arenas, int slots, size_t grad_off, size_
   p->slots = slots;
   p->n4 = (int)(n_floats / 4);
   p->world = arenas[0]->world;
+  p->has_mc = arenas[0]->mc != nullptr;
   B200_CHECK(cudaMalloc(&p->dev, sizeof(CommArgs) * slots));
   B200_CHECK(cudaMemcpy(p->dev, host.data(), sizeof(CommArgs) * slots, cudaMemcpyHostToDevice));
   *out = p;
@@ -261,7 +286,7 @@ int plan_from_arenas(SymmArena* const* arenas, int slots, size_t grad_off, size_
 }
 
 int default_blocks(const CommPlan* p, int mode) {
-  const int work = mode == 1 ? (p->n4 + p->world - 1) / p->world : p->n4;
+  const int work = mode >= 1 ? (p->n4 + p->world - 1) / p->world : p->n4;
   int nb = (work + 1023) / 1024;  // ~2 float4 per thread
   if (nb < 1) nb = 1;
   const int cap = p->slots > 1 ? max(1, (b200_sm_count() * 2) / p->slots) : 64;
@@ -270,14 +295,16 @@ int default_blocks(const CommPlan* p, int mode) {
 
 int run_plan(const CommPlan* p, int mode, int opt, uint32_t token, int nblocks, float rho, float eps, cudaStream_t s,
              int advance = -1, unsigned int* done_counter = nullptr) {
-  B200_REQUIRE(p && (mode == 0 || mode == 1), "comm run: bad plan/mode");
+  B200_REQUIRE(p && mode >= 0 && mode <= 2, "comm run: bad plan/mode");
+  B200_REQUIRE(mode != 2 || p->has_mc, "comm run: NVLS mode needs an arena with a multicast mapping");
   if (nblocks <= 0) nblocks = default_blocks(p, mode);
   B200_REQUIRE(nblocks <= SYMM_MAX_BLOCKS, "comm run: at most %d CTAs", SYMM_MAX_BLOCKS);
   dim3 grid(nblocks, p->slots);
   const CommArgs* tab = p->dev;
   void* args[] = {(void*)&tab, (void*)&token, (void*)&rho, (void*)&eps, (void*)&advance, (void*)&done_counter};
   const void* fn = mode == 0 ? (opt ? (const void*)fused_allreduce_kernel<0, true> : (const void*)fused_allreduce_kernel<0, false>)
-                             : (opt ? (const void*)fused_allreduce_kernel<1, true> : (const void*)fused_allreduce_kernel<1, false>);
+                 : mode == 1 ? (opt ? (const void*)fused_allreduce_kernel<1, true> : (const void*)fused_allreduce_kernel<1, false>)
+                             : (opt ? (const void*)fused_allreduce_kernel<2, true> : (const void*)fused_allreduce_kernel<2, false>);
   if (p->slots > 1) {
     // emulated ranks wait on each other inside one launch: all CTAs must be co-resident
     B200_CHECK(cudaLaunchCooperativeKernel(fn, grid, dim3(512), args, 0, s));

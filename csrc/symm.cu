@@ -58,6 +58,28 @@ extern "C" int b200_symm_import(void* arena, const void* all_handles) {
   return B200_OK;
 }
 
+// Wrap memory that somebody else made symmetric (e.g. torch.distributed._symmetric_memory, which also
+// provides an NVLS multicast mapping): peer_ptrs[q] = rank q's buffer as mapped here, mc_ptr = the
+// multicast alias or 0.  The buffers must hold payload_bytes + b200_symm_flag_bytes() and the flag
+// block must be zero.  Nothing is owned: b200_symm_destroy only frees the descriptor.
+extern "C" int b200_symm_wrap(int world, int rank, size_t payload_bytes, const uint64_t* peer_ptrs, uint64_t mc_ptr,
+                              void** out) {
+  B200_REQUIRE(out && peer_ptrs && world >= 1 && world <= SYMM_MAX_WORLD && rank >= 0 && rank < world,
+               "symm_wrap: bad arguments");
+  B200_REQUIRE(payload_bytes % 256 == 0, "symm_wrap: payload must be a multiple of 256 bytes");
+  SymmArena* a = new SymmArena();
+  a->world = world;
+  a->rank = rank;
+  a->payload = payload_bytes;
+  B200_CHECK(cudaGetDevice(&a->device));
+  for (int q = 0; q < world; ++q) a->peer[q] = (void*)peer_ptrs[q];
+  a->mc = (void*)mc_ptr;
+  *out = a;
+  return B200_OK;
+}
+
+extern "C" int b200_symm_has_multicast(void* arena) { return arena && ((SymmArena*)arena)->mc ? 1 : 0; }
+
 // W arenas on the current device, cross-linked as if they were W ranks (single-process tests)
 extern "C" int b200_symm_create_emulated(int world, size_t payload_bytes, void** arenas_out) {
   B200_REQUIRE(arenas_out && world >= 1 && world <= SYMM_MAX_WORLD, "symm_create_emulated: bad world %d", world);

@@ -17,5 +17,6 @@ struct SymmArena {
   bool opened[SYMM_MAX_WORLD] = {false};
   bool owns[SYMM_MAX_WORLD] = {false};
   bool emulated = false;
+  void* mc = nullptr;                      // multicast (NVLS) alias of all ranks' arenas, or null
   uint32_t* flags(int q) const { return (uint32_t*)((char*)peer[q] + payload); }
 };

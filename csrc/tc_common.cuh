@@ -46,6 +46,7 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
 }
 // Waits until the phase with the given parity has completed.  Bounded: ~seconds, then trap.
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+#pragma unroll 1
   for (uint32_t i = 0; i < (1u << 24); ++i)
     if (mbar_try_wait(bar, parity)) return;
   __trap();

@@ -169,6 +169,10 @@ int b200_symm_flag_bytes(void);
 int b200_symm_create(int world, int rank, size_t payload_bytes, void** arena_out);
 int b200_symm_export(void* arena, void* handle_out_host);            /* b200_symm_handle_bytes() bytes */
 int b200_symm_import(void* arena, const void* all_handles_host);      /* world handles, indexed by rank */
+/* adopt memory made symmetric elsewhere (e.g. torch symmetric memory); mc_ptr = NVLS multicast alias or 0 */
+int b200_symm_wrap(int world, int rank, size_t payload_bytes, const uint64_t* peer_ptrs_host, uint64_t mc_ptr,
+                   void** arena_out);
+int b200_symm_has_multicast(void* arena);
 int b200_symm_create_emulated(int world, size_t payload_bytes, void** arenas_out); /* W ranks on one GPU */
 int b200_symm_peer(void* arena, int rank, void** base_ptr);
 int b200_symm_pull(void* arena, int src_rank, size_t float_off, size_t n_floats, void* stream);
@@ -179,7 +183,7 @@ int b200_comm_plan_create(void* arena, size_t grad_off, size_t param_off, size_t
 int b200_comm_plan_create_emulated(void** arenas, int world, size_t grad_off, size_t param_off, size_t v_off,
                                    size_t u_off, size_t n_floats, int channel, const void** ctrls, void** plan_out);
 int b200_comm_plan_destroy(void* plan);
-/* mode 0 one-shot / 1 two-shot; opt 1 = fused 1/W + Adadelta, 0 = averaged all-reduce into param_off;
+/* mode 0 one-shot / 1 two-shot / 2 NVLS two-shot (multimem.ld_reduce + multimem.st; needs a multicast arena); opt 1 = fused 1/W + Adadelta, 0 = averaged all-reduce into param_off;
  * token 0 = derive from ctrl->step, else a caller token growing by 2 per call; nblocks 0 = automatic */
 int b200_comm_run(void* plan, int mode, int opt, unsigned int token, int nblocks, void* stream);
 /* engine created on the arena's buffers ([params][grads][sq_avg][acc_delta], ParamLayout.total floats each) */

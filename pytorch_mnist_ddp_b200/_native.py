@@ -133,6 +133,8 @@ _SIGNATURES = {
     "b200_symm_create": [_i, _i, ctypes.c_size_t, ctypes.POINTER(_vp)],
     "b200_symm_export": [_vp, _vp],
     "b200_symm_import": [_vp, _vp],
+    "b200_symm_wrap": [_i, _i, ctypes.c_size_t, ctypes.POINTER(ctypes.c_uint64), ctypes.c_uint64, ctypes.POINTER(_vp)],
+    "b200_symm_has_multicast": [_vp],
     "b200_symm_create_emulated": [_i, ctypes.c_size_t, ctypes.POINTER(_vp)],
     "b200_symm_peer": [_vp, _i, ctypes.POINTER(_vp)],
     "b200_symm_pull": [_vp, _i, ctypes.c_size_t, ctypes.c_size_t, _vp],

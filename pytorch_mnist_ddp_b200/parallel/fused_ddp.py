@@ -16,7 +16,8 @@ is rebuilt here on top of csrc/symm.cu and csrc/allreduce.cu:
 
 Reduction modes (``--comm``): ``oneshot`` (every rank reduces the whole bucket), ``twoshot``
 (reduce-scatter + sharded Adadelta + parameter all-gather), ``auto`` = two-shot for the 4.7 MB fc
-bucket when world >= 4, one-shot otherwise.  ``nccl`` keeps the reference's unfused structure
+bucket when world >= 4, one-shot otherwise; ``nvls`` = two-shot through the NVSwitch
+(``multimem.ld_reduce`` + ``multimem.st`` on a multicast mapping from torch symmetric memory).  ``nccl`` keeps the reference's unfused structure
 (ncclAllReduce + separate Adadelta) as the in-tree baseline.
 """
 from __future__ import annotations
@@ -30,7 +31,7 @@ import torch.distributed as dist
 from .. import _native as N
 from .dist import DistInfo
 
-ONESHOT, TWOSHOT = 0, 1
+ONESHOT, TWOSHOT, NVLS = 0, 1, 2
 
 
 class SymmetricArena:
@@ -59,6 +60,30 @@ class SymmetricArena:
             blob = bytes(everyone.cpu().numpy().tobytes())
             N.check(lib.b200_symm_import(h, blob))
             dist.barrier()
+        return arena
+
+    @classmethod
+    def create_torch(cls, info: DistInfo, payload_floats: int) -> "SymmetricArena":
+        """Arena backed by ``torch.distributed._symmetric_memory``: same peer mapping, plus the NVLS
+        multicast alias (``multimem.ld_reduce`` / ``multimem.st`` through the NVSwitch) when the driver and
+        fabric allow it.  Allocation and handle exchange are torch's; the kernels are ours."""
+        import torch.distributed._symmetric_memory as symm_mem
+        lib = N.lib()
+        payload_floats = (payload_floats + 63) // 64 * 64
+        flag_floats = lib.b200_symm_flag_bytes() // 4
+        dev = torch.device("cuda", torch.cuda.current_device())
+        buf = symm_mem.empty(payload_floats + flag_floats, dtype=torch.float32, device=dev)
+        buf.zero_()
+        hdl = symm_mem.rendezvous(buf, group=dist.group.WORLD)
+        torch.cuda.synchronize()
+        dist.barrier()
+        ptrs = (ctypes.c_uint64 * info.world_size)(*[int(p) for p in hdl.buffer_ptrs])
+        mc = int(getattr(hdl, "multicast_ptr", 0) or 0)
+        h = ctypes.c_void_p()
+        N.check(lib.b200_symm_wrap(info.world_size, info.rank, payload_floats * 4, ptrs, mc, ctypes.byref(h)))
+        arena = cls(h, info.world_size, info.rank, payload_floats)
+        arena._torch_keepalive = (buf, hdl)
+        arena.has_multicast = mc != 0
         return arena
 
     @classmethod
@@ -134,15 +159,14 @@ class FusedDataParallel:
     def __init__(self, info: DistInfo, comm: str = "auto") -> None:
         if comm not in ("auto", "oneshot", "twoshot", "nccl", "nvls"):
             raise ValueError(f"unknown comm mode {comm}")
-        if comm == "nvls":
-            raise N.NativeError("--comm nvls: multicast (NVLS) buffers are not wired up in this build; "
-                                "use twoshot (peer-to-peer reduce-scatter + parameter all-gather)")
         self.info, self.comm = info, comm
         w = info.world_size
         if comm == "auto":
             self.modes = (TWOSHOT if w >= 4 else ONESHOT, ONESHOT)
         elif comm == "twoshot":
             self.modes = (TWOSHOT, ONESHOT)
+        elif comm == "nvls":  # fc bucket through the switch (multimem), conv bucket one-shot P2P
+            self.modes = (NVLS, ONESHOT)
         else:
             self.modes = (ONESHOT, ONESHOT)
         self.mode = {"auto": f"auto({'twoshot' if self.modes[0] else 'oneshot'}+oneshot)"}.get(comm, comm)
@@ -152,7 +176,12 @@ class FusedDataParallel:
     def allocate(self, total_floats: int) -> Dict[str, int]:
         """Create the arena and return the raw pointers the engine must use for its flat buffers."""
         self.total = total_floats
-        self.arena = SymmetricArena.create(self.info, 4 * total_floats)
+        if self.comm == "nvls":
+            self.arena = SymmetricArena.create_torch(self.info, 4 * total_floats)
+            if not getattr(self.arena, "has_multicast", False):
+                raise N.NativeError("--comm nvls: this host/driver gave no multicast mapping (NVLS unavailable)")
+        else:
+            self.arena = SymmetricArena.create(self.info, 4 * total_floats)
         base = self.arena.base_ptr()
         t = total_floats * 4
         return {"params": base, "grads0": base + t, "grads1": base + t, "sq_avg": base + 2 * t,

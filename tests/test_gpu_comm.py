@@ -103,9 +103,11 @@ def _torchrun(nproc, script_args, timeout=600):
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs >= 2 GPUs")
-@pytest.mark.parametrize("comm", ["oneshot", "twoshot"])
+@pytest.mark.parametrize("comm", ["oneshot", "twoshot", "nvls"])
 def test_multi_gpu_ddp_equivalence(comm):
     """2 ranks x batch b without dropout == 1 rank x batch 2b ('DDP equivalence')."""
     res = _torchrun(2, ["tests/ddp_worker.py", "--comm", comm])
+    if comm == "nvls" and "NVLS unavailable" in res.stdout + res.stderr:
+        pytest.skip("no multicast mapping on this host")
     assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
     assert "DDP_EQUIVALENCE_OK" in res.stdout, res.stdout[-3000:]
