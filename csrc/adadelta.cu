@@ -61,6 +61,7 @@ adadelta_finalize_kernel(float* __restrict__ p, float* __restrict__ g, float* __
       const FinalizeSegs::Seg sg = segs.seg[k];
       const int e = off - sg.dst_off + 4 * col;
       if (sg.src && e >= 0 && e < sg.n) {
+#pragma unroll 8
         for (int q = slice; q < sg.nparts; q += 8) {
           const float4 x = *reinterpret_cast<const float4*>(sg.src + (size_t)q * sg.stride + e);
           acc.x += x.x; acc.y += x.y; acc.z += x.z; acc.w += x.w;

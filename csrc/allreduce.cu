@@ -189,6 +189,7 @@ finalize_bucket_kernel(const CommArgs* __restrict__ table, FinalizeSegs segs, fl
     const FinalizeSegs::Seg sg = segs.seg[k];
     const int e = off - sg.dst_off + 4 * col;
     if (sg.src && e >= 0 && e < sg.n) {
+#pragma unroll 8
       for (int p = slice; p < sg.nparts; p += 8) {
         const float4 v = *reinterpret_cast<const float4*>(sg.src + (size_t)p * sg.stride + e);
         acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;

@@ -96,12 +96,12 @@ conv1_wgrad_kernel(const uint8_t* __restrict__ images, const int32_t* __restrict
   for (int t = 0; t < 10; ++t) acc[t] = 0.f;
   constexpr int HALF = (H1 / 2) * W1;  // 338 pixels
   const int p0 = half * HALF;
-  for (int pb = g; pb < HALF; pb += 32) {
-    float d[4];
+  for (int pb = g; pb < HALF; pb += 64) {
+    float d[8];
 #pragma unroll
-    for (int u = 0; u < 4; ++u) d[u] = (pb + 8 * u < HALF) ? in[(p0 + pb + 8 * u) * C1 + o] : 0.f;  // 4 loads in flight
+    for (int u = 0; u < 8; ++u) d[u] = (pb + 8 * u < HALF) ? in[(p0 + pb + 8 * u) * C1 + o] : 0.f;  // 8 loads in flight
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
+    for (int u = 0; u < 8; ++u) {
       const int p = min(p0 + pb + 8 * u, H1 * W1 - 1);
       const int y = p / W1, xx = p - y * W1;
 #pragma unroll

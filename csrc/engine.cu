@@ -114,7 +114,8 @@ int enqueue_train(Engine* E, const uint8_t* images, const uint8_t* labels, const
     TRY(b200_unpool_dense(E->dp, E->amax, E->dy, E->db_part, db2, batch, s));
     if (E->use_tc & B200_TC_CONV2_V2) {
       TRY(b200_conv2_wgrad_tc2(E->dy, E->a1, E->c2_part, dw2, batch, s));
-      TRY(b200_conv2_dgrad_tc2(E->dy, P + c.offsets[2], E->a1, E->da1, batch, s));
+      if (E->use_tc & B200_TC_CONV2_V3) TRY(b200_conv2_dgrad_tc3(E->dy, P + c.offsets[2], E->a1, E->da1, batch, s));
+      else TRY(b200_conv2_dgrad_tc2(E->dy, P + c.offsets[2], E->a1, E->da1, batch, s));
       np2 = min(3 * batch, E->nsm);
     } else {
       TRY(b200_conv2_wgrad_tc(E->dy, E->a1, E->c2_part, dw2, batch, s));

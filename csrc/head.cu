@@ -129,8 +129,10 @@ head_wgrad_kernel(const float* __restrict__ h, const float* __restrict__ dlogits
   float s = 0.f;
   const int blk = blockIdx.x;
   if (blk < NCLS) {
+#pragma unroll 8
     for (int b = b0; b < b1; ++b) s = fmaf(dlogits[(size_t)b * DL + blk], h[(size_t)b * FC1_OUT + j], s);
   } else if (blk == NCLS) {
+#pragma unroll 8
     for (int b = b0; b < b1; ++b) s += dh[(size_t)b * FC1_OUT + j];
   } else {
     if (j < NCLS) for (int b = b0; b < b1; ++b) s += dlogits[(size_t)b * DL + j];

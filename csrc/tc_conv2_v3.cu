@@ -1,0 +1,207 @@
+// conv2 kernels, third generation: "kw-scatter" formulation to get off the shared-memory bound.
+//
+// Measured on B200 (profiles/README.md): an SS-mode 128 x N x 8 tf32 tcgen05.mma costs about
+// (A bytes + B bytes) / 64 cycles — the operand read from shared memory, not the tensor pipe, sets
+// the pace when N is small.  The v2 dgrad issues 72 MMAs of N = 32 per 128 output pixels (80 cycles
+// each for 16 cycles of tensor work).  Here the three kw taps are moved from the A side to the N side:
+//
+//   D[pixel (y,x')][(kw,i)] = sum_kh sum_o dY[y-kh][x'][o] * W[kh][kw][o][i]          (N = 96)
+//   da1[y][x][i]            = relu'(a1) * sum_kw D[(y, x-kw)][(kw,i)]
+//
+// so one 128 x 96 x 8 MMA replaces three 128 x 32 x 8 ones and re-uses the same A tile; the kh taps
+// are still accumulated by the tensor core through row-shifted views of the dY patch; the kw sum
+// becomes two warp shuffles per value in the epilogue, because a tile is 4 output rows x 32 pixels
+// and a warp holds exactly one row (lane = x).  With the patch pitch padded to 32 pixels such a tile
+// is a plain contiguous 16 KiB K-major operand.  24 MMAs per tile instead of 72.
+#include <map>
+#include <mutex>
+#include <tuple>
+
+#include "common.cuh"
+#include "tc_common.cuh"
+
+using namespace tc;
+using namespace net;
+
+namespace {
+
+constexpr int TAP_BYTES = 64 * 128;
+constexpr int P_ROWS = 18, P_PITCH = 32;
+constexpr int ROW_BYTES = P_PITCH * 128;
+constexpr int PATCH_BYTES = P_ROWS * ROW_BYTES;
+constexpr int DG_SMEM = 9 * TAP_BYTES + 2 * PATCH_BYTES + 1024;
+
+// Item = (image, half): half 0 -> output rows 0..15 (4 tiles), half 1 -> rows 16..25 (3 tiles, the last
+// one half empty).  The patch holds dY rows y0-2 .. y0+15, columns 0..31 (24 real, zero beyond).
+__global__ void __launch_bounds__(192, 1)
+conv2_dgrad_tc3_kernel(const __grid_constant__ CUtensorMap mapDY, const __grid_constant__ CUtensorMap mapW,
+                       const float* __restrict__ a1, float* __restrict__ da1, int nitems) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  uint8_t* wsm = smem;                     // [kh][kw][64 o][32 i], 32B-atom swizzle: N-major B operand
+  uint8_t* patch = smem + 9 * TAP_BYTES;   // [2 channel chunks][18][32][128 B]
+  __shared__ __align__(8) uint64_t w_bar, pfull[2], pempty[2], tfull[4], tempty[4];
+  __shared__ uint32_t tmem_base_smem;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) {
+    tma_prefetch_desc(&mapDY);
+    tma_prefetch_desc(&mapW);
+    mbar_init(&w_bar, 1);
+    for (int i = 0; i < 2; ++i) { mbar_init(&pfull[i], 1); mbar_init(&pempty[i], 1); }
+    for (int i = 0; i < 4; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 4); }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(&tmem_base_smem, 512);  // 4 accumulator slots of 128 columns (96 used)
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_smem;
+  const int my_items = (nitems - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+
+  if (warp == 0) {
+    const bool leader = elect_one();
+    if (leader) mbar_expect_tx(&w_bar, 9 * TAP_BYTES);
+    for (int t = 0; t < 9; ++t)
+      if (leader) tma_load_2d(wsm + t * TAP_BYTES, &mapW, &w_bar, 0, t * 64);
+    for (int it = 0; it < my_items; ++it) {
+      const int item = blockIdx.x + it * gridDim.x, n = item >> 1, y0 = (item & 1) * 16;
+      for (int kc = 0; kc < 2; ++kc) {
+        mbar_wait(&pempty[kc], (it & 1) ^ 1);
+        if (leader) mbar_expect_tx(&pfull[kc], PATCH_BYTES);
+        for (int r = 0; r < P_ROWS; ++r)
+          if (leader) tma_load_4d(patch + kc * PATCH_BYTES + r * ROW_BYTES, &mapDY, &pfull[kc], kc * 32, 0, y0 - 2 + r, n);
+      }
+    }
+  } else if (warp == 1) {
+    const bool leader = elect_one();
+    constexpr uint32_t idesc = idesc_tf32(128, 96, 0, 1);
+    mbar_wait(&w_bar, 0);
+    int tc_ = 0;  // running tile counter -> TMEM slot
+    for (int it = 0; it < my_items; ++it) {
+      const int ntile = ((blockIdx.x + it * gridDim.x) & 1) ? 3 : 4;
+      // chunk-major order: all tiles of the item consume channel chunk 0, then chunk 1
+      for (int kc = 0; kc < 2; ++kc) {
+        mbar_wait(&pfull[kc], it & 1);
+        tc_fence_after();
+        const uint32_t pb = smem_u32(patch + kc * PATCH_BYTES);
+        for (int t = 0; t < ntile; ++t) {
+          const int slot = (tc_ + t) & 3;
+          if (kc == 0) {
+            mbar_wait(&tempty[slot], (((tc_ + t) >> 2) & 1) ^ 1);
+            tc_fence_after();
+          }
+          const uint32_t d = tmem_base + slot * 128;
+#pragma unroll
+          for (int kh = 0; kh < 3; ++kh) {
+            const uint32_t sa = pb + (uint32_t)((4 * t + 2 - kh) * ROW_BYTES);
+            const uint32_t sw = smem_u32(wsm + kh * 3 * TAP_BYTES + kc * 4096);
+#pragma unroll
+            for (int kk = 0; kk < 4; ++kk)
+              if (leader)
+                umma_tf32(d, desc_kmajor(sa + kk * 32), desc_mnmajor(sw + kk * 1024, TAP_BYTES), idesc,
+                          (kc | kh | kk) != 0);
+          }
+          if (kc == 1 && leader) umma_commit(&tfull[slot]);
+        }
+        if (leader) umma_commit(&pempty[kc]);
+      }
+      tc_ += ntile;
+    }
+  } else {
+    const int q = warp & 3;
+    int tc_ = 0;
+    for (int it = 0; it < my_items; ++it) {
+      const int item = blockIdx.x + it * gridDim.x, n = item >> 1, half = item & 1, y0 = half * 16;
+      const int ntile = half ? 3 : 4;
+      for (int t = 0; t < ntile; ++t) {
+        const int slot = (tc_ + t) & 3;
+        mbar_wait(&tfull[slot], ((tc_ + t) >> 2) & 1);
+        tc_fence_after();
+        float v0[32], v1[32], v2[32];
+        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + slot * 128;
+        tmem_ld32(taddr, v0);
+        tmem_ld32(taddr + 32, v1);
+        tmem_ld32(taddr + 64, v2);
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tempty[slot]);
+        // da1[y][x] = D[x][kw=0] + D[x-1][kw=1] + D[x-2][kw=2]   (lane = x; columns >= 24 of D are zero)
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          const float s1 = __shfl_up_sync(0xffffffffu, v1[j], 1);
+          const float s2 = __shfl_up_sync(0xffffffffu, v2[j], 2);
+          v0[j] += (lane >= 1 ? s1 : 0.f) + (lane >= 2 ? s2 : 0.f);
+        }
+        const int y = y0 + 4 * t + q, x = lane;
+        if (y < H1 && x < W1) {
+          const size_t e = (((size_t)n * H1 + y) * W1 + x) * C1;
+#pragma unroll
+          for (int j = 0; j < 32; j += 4) {
+            const float4 a = *reinterpret_cast<const float4*>(a1 + e + j);
+            *reinterpret_cast<float4*>(da1 + e + j) =
+                make_float4(a.x > 0.f ? v0[j] : 0.f, a.y > 0.f ? v0[j + 1] : 0.f, a.z > 0.f ? v0[j + 2] : 0.f,
+                            a.w > 0.f ? v0[j + 3] : 0.f);
+          }
+        }
+      }
+      tc_ += ntile;
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, 512);
+}
+
+struct Key {
+  const void* p; int batch, kind;
+  bool operator<(const Key& o) const { return std::tie(p, batch, kind) < std::tie(o.p, o.batch, o.kind); }
+};
+std::map<Key, CUtensorMap> g_maps;
+std::mutex g_mu;
+
+// kind 0: dY patch row (K-major, 32 channels x 32 px x 1 row)   1: weights (32B-atom swizzle, N-major)
+int get_map(const float* p, int batch, int kind, CUtensorMap* out) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  Key key{p, batch, kind};
+  auto it = g_maps.find(key);
+  if (it != g_maps.end()) { *out = it->second; return B200_OK; }
+  CUtensorMap m;
+  int r;
+  if (kind == 0) {
+    uint64_t dims[4] = {64, 24, 24, (uint64_t)batch}, strides[3] = {256, 24 * 256, 576 * 256};
+    uint32_t box[4] = {32, P_PITCH, 1, 1};
+    r = tcmap::encode(&m, p, 4, dims, strides, box, 0);
+  } else {
+    uint64_t dims[2] = {32, 576}, strides[1] = {128};
+    uint32_t box[2] = {32, 64};
+    r = tcmap::encode(&m, p, 2, dims, strides, box, 1);
+  }
+  if (r != B200_OK) return r;
+  g_maps[key] = m;
+  *out = m;
+  return B200_OK;
+}
+
+}  // namespace
+
+extern "C" int b200_conv2_dgrad_tc3(const float* dy, const float* w, const float* a1, float* da1, int batch,
+                                    void* stream) {
+  B200_REQUIRE(batch > 0, "conv2_dgrad_tc3: batch must be > 0");
+  CUtensorMap md, mw;
+  int r = get_map(dy, batch, 0, &md);
+  if (r != B200_OK) return r;
+  r = get_map(w, 0, 1, &mw);
+  if (r != B200_OK) return r;
+  static bool attr = false;
+  if (!attr) {
+    B200_CHECK(cudaFuncSetAttribute(conv2_dgrad_tc3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, DG_SMEM));
+    attr = true;
+  }
+  const int nitems = 2 * batch;
+  const int grid = min(nitems, b200_sm_count());
+  conv2_dgrad_tc3_kernel<<<grid, 192, DG_SMEM, (cudaStream_t)stream>>>(md, mw, a1, da1, nitems);
+  b200_count_launch();
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}

@@ -86,6 +86,8 @@ int b200_conv2_fwd_tc(const float* a1, const float* w, const float* bias, const 
 int b200_conv2_fwd_tc2(const float* a1, const float* w, const float* bias, const void* ctrl, float* pooled,
                        uint8_t* amax, int batch, void* stream);
 int b200_conv2_dgrad_tc2(const float* dy, const float* w, const float* a1, float* da1, int batch, void* stream);
+/* third generation dgrad: the three kw taps sit on the N side of the MMA (128x96x8), summed by shuffles */
+int b200_conv2_dgrad_tc3(const float* dy, const float* w, const float* a1, float* da1, int batch, void* stream);
 int b200_conv2_wgrad_tc2(const float* dy, const float* a1, float* part, float* dw, int batch, void* stream);
 /* implicit-GEMM dgrad from the dense dY [B][24][24][64]; epilogue applies conv1's ReLU mask */
 int b200_conv2_dgrad_tc(const float* dy, const float* w, const float* a1, float* da1, int batch, void* stream);
@@ -112,7 +114,7 @@ typedef struct B200EngineConfig {
   int world, rank;
   unsigned long long seed;
   int use_tc;           /* bit mask: 1 conv2 fwd, 2 fc1 fwd, 4 fc1 bwd, 8 conv2 bwd on tcgen05; 16: patch-view (v2)
-                           conv2 kernels; 0: CUDA-core kernels everywhere */
+                           conv2 kernels, 32: kw-scatter (v3) dgrad; 0: CUDA-core kernels everywhere */
   int train_n, test_n;  /* dataset sizes (samples) */
   long param_floats;    /* ParamLayout.total */
   long offsets[8];      /* conv1.w, conv1.b, conv2.w, conv2.b, fc1.w, fc1.b, fc2.w, fc2.b (floats) */

@@ -29,8 +29,8 @@ from .utils.data import MnistSplit
  BUF_DLOGITS, BUF_DH, BUF_DP, BUF_DA1, BUF_LOSS_I, BUF_LOSS_RING, BUF_CTRL, BUF_LOGP, BUF_STAGE_IMG,
  BUF_STAGE_LBL, BUF_FC1_PART) = range(20)
 LOSS_RING = 1024
-TC_CONV2_FWD, TC_FC1_FWD, TC_FC1_BWD, TC_CONV2_BWD, TC_CONV2_V2 = 1, 2, 4, 8, 16
-TC_ALL = 31
+TC_CONV2_FWD, TC_FC1_FWD, TC_FC1_BWD, TC_CONV2_BWD, TC_CONV2_V2, TC_CONV2_V3 = 1, 2, 4, 8, 16, 32
+TC_ALL = 63
 DEFAULT_TC = TC_ALL
 
 

@@ -85,7 +85,8 @@ def conv2_dgrad(dp, amax, w, a1, tc: bool = False) -> torch.Tensor:
     da1 = torch.empty(batch, 26, 26, 32, device="cuda")
     if tc:
         dy = unpool_dense(dp, amax)
-        fn = N.lib().b200_conv2_dgrad_tc2 if tc == 2 else N.lib().b200_conv2_dgrad_tc
+        L = N.lib()
+        fn = {2: L.b200_conv2_dgrad_tc2, 3: L.b200_conv2_dgrad_tc3}.get(tc, L.b200_conv2_dgrad_tc)
         N.check(fn(_p(dy), _p(w), _p(a1), _p(da1), batch, _s()))
     else:
         N.check(N.lib().b200_conv2_dgrad_simt(_p(dp), _p(amax), _p(w), _p(a1), _p(da1), batch, _s()))
@@ -99,7 +100,7 @@ def conv2_wgrad(dp, amax, a1, tc: bool = False) -> Tuple[torch.Tensor, torch.Ten
     dw, db = torch.empty(9, 64, 32, device="cuda"), torch.empty(64, device="cuda")
     if tc:
         dy, db = unpool_dense(dp, amax, with_db=True)
-        fn = L.b200_conv2_wgrad_tc2 if tc == 2 else L.b200_conv2_wgrad_tc
+        fn = L.b200_conv2_wgrad_tc2 if tc in (2, 3) else L.b200_conv2_wgrad_tc
         N.check(fn(_p(dy), _p(a1), _p(part), _p(dw), batch, _s()))
     else:
         N.check(L.b200_conv2_wgrad_simt(_p(dp), _p(amax), _p(a1), _p(part), _p(dw), _p(db), batch, _s()))

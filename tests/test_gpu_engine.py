@@ -42,10 +42,10 @@ def _norm(u8):
 
 def _tc_masks():
     from pytorch_mnist_ddp_b200 import _native as N
-    return [0, 15, 31] if N.lib().b200_has_tc() else [0]
+    return [0, 15, 31, 63] if N.lib().b200_has_tc() else [0]
 
 
-@pytest.mark.parametrize("use_tc", [0, 15, 31])
+@pytest.mark.parametrize("use_tc", [0, 15, 31, 63])
 @pytest.mark.parametrize("batch", [64, 200])
 def test_train_step_matches_torch_without_dropout(use_tc, batch):
     if use_tc not in _tc_masks():

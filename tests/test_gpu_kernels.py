@@ -193,7 +193,7 @@ def test_head_eval_and_train(ops, batch):
 
 
 @pytest.mark.parametrize("batch", [1, 7, 64])
-@pytest.mark.parametrize("tc", [False, True, 2])
+@pytest.mark.parametrize("tc", [False, True, 2, 3])
 def test_conv2_backward(ops, batch, tc):
     _need_tc(tc)
     net = _net()
