@@ -64,7 +64,9 @@ int enqueue_forward(Engine* E, const uint8_t* images, const uint8_t* labels, con
   const B200EngineConfig& c = E->cfg;
   float* P = E->P;
   TRY(b200_conv1_fwd(images, idx, ctrl, P + c.offsets[0], P + c.offsets[1], E->a1, batch, s));
-  if ((E->use_tc & B200_TC_CONV2_FWD) && (E->use_tc & B200_TC_CONV2_V2))
+  if ((E->use_tc & B200_TC_CONV2_FWD) && (E->use_tc & B200_TC_CONV2_V3))
+    TRY(b200_conv2_fwd_tc3(E->a1, P + c.offsets[2], P + c.offsets[3], ctrl, E->pooled, E->amax, batch, s));
+  else if ((E->use_tc & B200_TC_CONV2_FWD) && (E->use_tc & B200_TC_CONV2_V2))
     TRY(b200_conv2_fwd_tc2(E->a1, P + c.offsets[2], P + c.offsets[3], ctrl, E->pooled, E->amax, batch, s));
   else if (E->use_tc & B200_TC_CONV2_FWD)
     TRY(b200_conv2_fwd_tc(E->a1, P + c.offsets[2], P + c.offsets[3], ctrl, E->pooled, E->amax, batch, s));

@@ -33,7 +33,7 @@ constexpr int DG_SMEM = 9 * TAP_BYTES + 2 * PATCH_BYTES + 1024;
 
 // Item = (image, half): half 0 -> output rows 0..15 (4 tiles), half 1 -> rows 16..25 (3 tiles, the last
 // one half empty).  The patch holds dY rows y0-2 .. y0+15, columns 0..31 (24 real, zero beyond).
-__global__ void __launch_bounds__(192, 1)
+__global__ void __launch_bounds__(320, 1)
 conv2_dgrad_tc3_kernel(const __grid_constant__ CUtensorMap mapDY, const __grid_constant__ CUtensorMap mapW,
                        const float* __restrict__ a1, float* __restrict__ da1, int nitems) {
   extern __shared__ uint8_t smem_raw[];
@@ -49,7 +49,7 @@ conv2_dgrad_tc3_kernel(const __grid_constant__ CUtensorMap mapDY, const __grid_c
     tma_prefetch_desc(&mapW);
     mbar_init(&w_bar, 1);
     for (int i = 0; i < 2; ++i) { mbar_init(&pfull[i], 1); mbar_init(&pempty[i], 1); }
-    for (int i = 0; i < 4; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 4); }
+    for (int i = 0; i < 4; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 8); }
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc(&tmem_base_smem, 512);  // 4 accumulator slots of 128 columns (96 used)
@@ -109,7 +109,8 @@ conv2_dgrad_tc3_kernel(const __grid_constant__ CUtensorMap mapDY, const __grid_c
       tc_ += ntile;
     }
   } else {
-    const int q = warp & 3;
+    // 8 epilogue warps: warp pairs (w, w+4) share a TMEM sub-partition and split the 32 channels
+    const int q = warp & 3, hc = (warp - 2) >> 2;
     int tc_ = 0;
     for (int it = 0; it < my_items; ++it) {
       const int item = blockIdx.x + it * gridDim.x, n = item >> 1, half = item & 1, y0 = half * 16;
@@ -118,26 +119,26 @@ conv2_dgrad_tc3_kernel(const __grid_constant__ CUtensorMap mapDY, const __grid_c
         const int slot = (tc_ + t) & 3;
         mbar_wait(&tfull[slot], ((tc_ + t) >> 2) & 1);
         tc_fence_after();
-        float v0[32], v1[32], v2[32];
-        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + slot * 128;
-        tmem_ld32(taddr, v0);
-        tmem_ld32(taddr + 32, v1);
-        tmem_ld32(taddr + 64, v2);
+        float v0[16], v1[16], v2[16];
+        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + slot * 128 + hc * 16;
+        tmem_ld16(taddr, v0);
+        tmem_ld16(taddr + 32, v1);
+        tmem_ld16(taddr + 64, v2);
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&tempty[slot]);
         // da1[y][x] = D[x][kw=0] + D[x-1][kw=1] + D[x-2][kw=2]   (lane = x; columns >= 24 of D are zero)
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
+        for (int j = 0; j < 16; ++j) {
           const float s1 = __shfl_up_sync(0xffffffffu, v1[j], 1);
           const float s2 = __shfl_up_sync(0xffffffffu, v2[j], 2);
           v0[j] += (lane >= 1 ? s1 : 0.f) + (lane >= 2 ? s2 : 0.f);
         }
         const int y = y0 + 4 * t + q, x = lane;
         if (y < H1 && x < W1) {
-          const size_t e = (((size_t)n * H1 + y) * W1 + x) * C1;
+          const size_t e = (((size_t)n * H1 + y) * W1 + x) * C1 + hc * 16;
 #pragma unroll
-          for (int j = 0; j < 32; j += 4) {
+          for (int j = 0; j < 16; j += 4) {
             const float4 a = *reinterpret_cast<const float4*>(a1 + e + j);
             *reinterpret_cast<float4*>(da1 + e + j) =
                 make_float4(a.x > 0.f ? v0[j] : 0.f, a.y > 0.f ? v0[j + 1] : 0.f, a.z > 0.f ? v0[j + 2] : 0.f,
@@ -146,6 +147,184 @@ conv2_dgrad_tc3_kernel(const __grid_constant__ CUtensorMap mapDY, const __grid_c
         }
       }
       tc_ += ntile;
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, 512);
+}
+
+// =============================================================================================
+// forward v3:  D[(y,x')][(kw,o)] = sum_kh sum_i a1[y+kh][x'][i] * W[kh][kw][o][i]      (N = 192)
+//              out[y][x][o]      = sum_kw D[(y, x+kw)][(kw,o)]   -> bias, ReLU, 2x2 max-pool, dropout
+// Item = (image, x-half): a 26-row x 16-pixel patch (columns 0..15 or 10..25, 52 KB, pitch 16 pixels)
+// feeds three 8-row x 16-pixel tiles; a tile is a contiguous 16 KiB K-major operand at row (8*ty + kh).
+// The B operand of one kh is simply the native weight block [kw][o][i] = 192 rows of 128 bytes.
+// 12 MMAs of 128x192x8 per tile instead of 36 of 128x64x8.  A warp holds two tile rows (lanes 0..15 =
+// row 2q, lanes 16..31 = row 2q+1), so the kw-sum is a shuffle-down by 1 and 2 and the 2x2 pool is the
+// (lane^1, lane^16) neighbourhood.  14 of the 16 columns are valid outputs; the two halves overlap.
+// =============================================================================================
+constexpr int F_PITCH = 16, F_ROWS = 26;
+constexpr int F_ROW_BYTES = F_PITCH * 128;             // 2 KiB
+constexpr int F_PATCH_BYTES = F_ROWS * F_ROW_BYTES;    // 53,248
+constexpr int F3_SMEM = 9 * TAP_BYTES + 2 * F_PATCH_BYTES + 1024;
+
+// 32 channels of one output pixel per lane -> 2x2 max-pool over (lane^1, lane^16) -> 8 channels of one
+// pooled pixel per lane (channel offset c0) -> bias, ReLU, dropout, store.
+__device__ __forceinline__ void pool32_store(const float (&v)[32], int lane, int oc, const float* bias_s, int train,
+                                             unsigned long long seed, unsigned long long step, uint32_t e_pixel,
+                                             bool store, float* __restrict__ pooled, uint8_t* __restrict__ amax) {
+  const bool b0 = lane & 1, b4 = (lane >> 4) & 1;
+  float m1[16];
+  uint32_t dxmask = 0;
+#pragma unroll
+  for (int j = 0; j < 16; ++j) {
+    const float mine = b0 ? v[16 + j] : v[j], send = b0 ? v[j] : v[16 + j];
+    const float recv = __shfl_xor_sync(0xffffffffu, send, 1);
+    const float ev = b0 ? recv : mine, od = b0 ? mine : recv;
+    const bool gt = od > ev;  // strict: first maximum wins
+    m1[j] = gt ? od : ev;
+    dxmask |= (uint32_t)gt << j;
+  }
+  const uint32_t dx_other = __shfl_xor_sync(0xffffffffu, dxmask, 16);
+  float m2[8];
+  uint32_t am[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const float mine = b4 ? m1[8 + j] : m1[j], send = b4 ? m1[j] : m1[8 + j];
+    const float recv = __shfl_xor_sync(0xffffffffu, send, 16);
+    const int jj = (b4 ? 8 : 0) + j;
+    const uint32_t dxm = (dxmask >> jj) & 1u, dxo = (dx_other >> jj) & 1u;
+    const float top = b4 ? recv : mine, bot = b4 ? mine : recv;
+    const uint32_t dxt = b4 ? dxo : dxm, dxb = b4 ? dxm : dxo;
+    const bool gt = bot > top;
+    m2[j] = gt ? bot : top;
+    am[j] = gt ? (2u + dxb) : dxt;
+  }
+  if (!store) return;
+  const int c0 = oc * 32 + (b0 ? 16 : 0) + (b4 ? 8 : 0);
+  const uint32_t e = e_pixel + c0;
+#pragma unroll
+  for (int g4 = 0; g4 < 2; ++g4) {
+    float o[4];
+#pragma unroll
+    for (int c = 0; c < 4; ++c) o[c] = fmaxf(m2[g4 * 4 + c] + bias_s[c0 + g4 * 4 + c], 0.f);
+    if (train & 2) {
+      const uint4 r = dropout_bits4(seed, step, 1u, (e >> 2) + g4);
+      const float sc = 1.0f / (1.0f - P_DROP1);
+      o[0] = dropout_keep(r.x, DROP1_THRESH) ? o[0] * sc : 0.f;
+      o[1] = dropout_keep(r.y, DROP1_THRESH) ? o[1] * sc : 0.f;
+      o[2] = dropout_keep(r.z, DROP1_THRESH) ? o[2] * sc : 0.f;
+      o[3] = dropout_keep(r.w, DROP1_THRESH) ? o[3] * sc : 0.f;
+    }
+    *reinterpret_cast<float4*>(pooled + e + g4 * 4) = make_float4(o[0], o[1], o[2], o[3]);
+  }
+  uint2 pk;
+  pk.x = am[0] | (am[1] << 8) | (am[2] << 16) | (am[3] << 24);
+  pk.y = am[4] | (am[5] << 8) | (am[6] << 16) | (am[7] << 24);
+  *reinterpret_cast<uint2*>(amax + e) = pk;
+}
+
+__global__ void __launch_bounds__(320, 1)
+conv2_fwd_tc3_kernel(const __grid_constant__ CUtensorMap mapP, const __grid_constant__ CUtensorMap mapW,
+                     const float* __restrict__ bias, const B200Ctrl* __restrict__ ctrl, float* __restrict__ pooled,
+                     uint8_t* __restrict__ amax, int nitems) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  uint8_t* wsm = smem;                        // [kh][kw][64 o][32 i]: per kh a K-major 192 x 32 B operand
+  uint8_t* patch = smem + 9 * TAP_BYTES;      // [2][26 rows][16 px][128 B]
+  __shared__ __align__(8) uint64_t w_bar, pfull[2], pempty[2], tfull[2], tempty[2];
+  __shared__ uint32_t tmem_base_smem;
+  __shared__ float bias_s[C2];
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) {
+    tma_prefetch_desc(&mapP);
+    tma_prefetch_desc(&mapW);
+    mbar_init(&w_bar, 1);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&pfull[i], 1); mbar_init(&pempty[i], 1);
+      mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 8);
+    }
+    fence_barrier_init();
+  }
+  if (threadIdx.x < C2) bias_s[threadIdx.x] = bias[threadIdx.x];
+  if (warp == 1) tmem_alloc(&tmem_base_smem, 512);  // 2 accumulator slots of 256 columns (192 used)
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_smem;
+  const int my_items = (nitems - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+
+  if (warp == 0) {
+    const bool leader = elect_one();
+    if (leader) mbar_expect_tx(&w_bar, 9 * TAP_BYTES);
+    for (int t = 0; t < 9; ++t)
+      if (leader) tma_load_2d(wsm + t * TAP_BYTES, &mapW, &w_bar, 0, t * 64);
+    for (int it = 0; it < my_items; ++it) {
+      const int item = blockIdx.x + it * gridDim.x, n = item >> 1, X0 = (item & 1) * 10, buf = it & 1;
+      mbar_wait(&pempty[buf], ((it >> 1) & 1) ^ 1);
+      if (leader) mbar_expect_tx(&pfull[buf], F_PATCH_BYTES);
+      for (int r = 0; r < F_ROWS; ++r)
+        if (leader) tma_load_4d(patch + buf * F_PATCH_BYTES + r * F_ROW_BYTES, &mapP, &pfull[buf], 0, X0, r, n);
+    }
+  } else if (warp == 1) {
+    const bool leader = elect_one();
+    constexpr uint32_t idesc = idesc_tf32(128, 192, 0, 0);
+    mbar_wait(&w_bar, 0);
+    int tc_ = 0;
+    for (int it = 0; it < my_items; ++it) {
+      const int buf = it & 1;
+      mbar_wait(&pfull[buf], (it >> 1) & 1);
+      tc_fence_after();
+      const uint32_t pb = smem_u32(patch + buf * F_PATCH_BYTES);
+      for (int ty = 0; ty < 3; ++ty, ++tc_) {
+        const int slot = tc_ & 1;
+        mbar_wait(&tempty[slot], ((tc_ >> 1) & 1) ^ 1);
+        tc_fence_after();
+        const uint32_t d = tmem_base + slot * 256;
+#pragma unroll
+        for (int kh = 0; kh < 3; ++kh) {
+          const uint32_t sa = pb + (uint32_t)((ty * 8 + kh) * F_ROW_BYTES);
+          const uint32_t sw = smem_u32(wsm + kh * 3 * TAP_BYTES);
+#pragma unroll
+          for (int kk = 0; kk < 4; ++kk)
+            if (leader) umma_tf32(d, desc_kmajor(sa + kk * 32), desc_kmajor(sw + kk * 32), idesc, (kh | kk) != 0);
+        }
+        if (leader) umma_commit(&tfull[slot]);
+      }
+      if (leader) umma_commit(&pempty[buf]);
+    }
+  } else {
+    // 8 epilogue warps: warp pairs (w, w+4) share a TMEM sub-partition; each takes 32 of the 64 channels
+    const int q = warp & 3, oc = (warp - 2) >> 2;
+    const int train = ctrl->train;
+    const unsigned long long seed = ctrl->seed, step = ctrl->step;
+    const int lx = lane & 15;
+    int tc_ = 0;
+    for (int it = 0; it < my_items; ++it) {
+      const int item = blockIdx.x + it * gridDim.x, n = item >> 1, half = item & 1, X0 = half * 10;
+      // half 0 stores output columns 0..11 (local 0..11), half 1 columns 12..23 (local 2..13)
+      const bool store = half ? (lx >= 2 && lx < 14) : (lx < 12);
+      for (int ty = 0; ty < 3; ++ty, ++tc_) {
+        const int slot = tc_ & 1;
+        mbar_wait(&tfull[slot], (tc_ >> 1) & 1);
+        tc_fence_after();
+        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + slot * 256;
+        const int ph = ty * 4 + q, pw = (X0 + lx) >> 1;
+        const uint32_t e_pixel = ((uint32_t)(n * HP + ph) * WP + pw) * C2;
+        float v0[32], v1[32], v2[32];
+        tmem_ld32(taddr + oc * 32, v0);        // kw = 0
+        tmem_ld32(taddr + 64 + oc * 32, v1);   // kw = 1
+        tmem_ld32(taddr + 128 + oc * 32, v2);  // kw = 2
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tempty[slot]);
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          v0[j] += __shfl_down_sync(0xffffffffu, v1[j], 1) + __shfl_down_sync(0xffffffffu, v2[j], 2);
+        pool32_store(v0, lane, oc, bias_s, train, seed, step, e_pixel, store, pooled, amax);
+      }
     }
   }
   tc_fence_before();
@@ -172,6 +351,14 @@ int get_map(const float* p, int batch, int kind, CUtensorMap* out) {
     uint64_t dims[4] = {64, 24, 24, (uint64_t)batch}, strides[3] = {256, 24 * 256, 576 * 256};
     uint32_t box[4] = {32, P_PITCH, 1, 1};
     r = tcmap::encode(&m, p, 4, dims, strides, box, 0);
+  } else if (kind == 2) {  // a1 patch row for the forward: 32 channels x 16 px x 1 row
+    uint64_t dims[4] = {32, 26, 26, (uint64_t)batch}, strides[3] = {128, 26 * 128, 676 * 128};
+    uint32_t box[4] = {32, F_PITCH, 1, 1};
+    r = tcmap::encode(&m, p, 4, dims, strides, box, 0);
+  } else if (kind == 3) {  // weights, K-major (plain 128B swizzle)
+    uint64_t dims[2] = {32, 576}, strides[1] = {128};
+    uint32_t box[2] = {32, 64};
+    r = tcmap::encode(&m, p, 2, dims, strides, box, 0);
   } else {
     uint64_t dims[2] = {32, 576}, strides[1] = {128};
     uint32_t box[2] = {32, 64};
@@ -200,7 +387,29 @@ extern "C" int b200_conv2_dgrad_tc3(const float* dy, const float* w, const float
   }
   const int nitems = 2 * batch;
   const int grid = min(nitems, b200_sm_count());
-  conv2_dgrad_tc3_kernel<<<grid, 192, DG_SMEM, (cudaStream_t)stream>>>(md, mw, a1, da1, nitems);
+  conv2_dgrad_tc3_kernel<<<grid, 320, DG_SMEM, (cudaStream_t)stream>>>(md, mw, a1, da1, nitems);
+  b200_count_launch();
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+extern "C" int b200_conv2_fwd_tc3(const float* a1, const float* w, const float* bias, const void* ctrl, float* pooled,
+                                  uint8_t* amax, int batch, void* stream) {
+  B200_REQUIRE(batch > 0, "conv2_fwd_tc3: batch must be > 0");
+  CUtensorMap mp, mw;
+  int r = get_map(a1, batch, 2, &mp);
+  if (r != B200_OK) return r;
+  r = get_map(w, 0, 3, &mw);
+  if (r != B200_OK) return r;
+  static bool attr = false;
+  if (!attr) {
+    B200_CHECK(cudaFuncSetAttribute(conv2_fwd_tc3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, F3_SMEM));
+    attr = true;
+  }
+  const int nitems = 2 * batch;
+  const int grid = min(nitems, b200_sm_count());
+  conv2_fwd_tc3_kernel<<<grid, 320, F3_SMEM, (cudaStream_t)stream>>>(mp, mw, bias, (const B200Ctrl*)ctrl, pooled, amax,
+                                                                    nitems);
   b200_count_launch();
   B200_LAUNCH_CHECK();
   return B200_OK;

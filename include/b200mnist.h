@@ -86,6 +86,9 @@ int b200_conv2_fwd_tc(const float* a1, const float* w, const float* bias, const 
 int b200_conv2_fwd_tc2(const float* a1, const float* w, const float* bias, const void* ctrl, float* pooled,
                        uint8_t* amax, int batch, void* stream);
 int b200_conv2_dgrad_tc2(const float* dy, const float* w, const float* a1, float* da1, int batch, void* stream);
+/* third generation forward: kw taps on the N side (128x192x8 MMAs), kw-sum + pooling by warp shuffles */
+int b200_conv2_fwd_tc3(const float* a1, const float* w, const float* bias, const void* ctrl, float* pooled,
+                       uint8_t* amax, int batch, void* stream);
 /* third generation dgrad: the three kw taps sit on the N side of the MMA (128x96x8), summed by shuffles */
 int b200_conv2_dgrad_tc3(const float* dy, const float* w, const float* a1, float* da1, int batch, void* stream);
 int b200_conv2_wgrad_tc2(const float* dy, const float* a1, float* part, float* dw, int batch, void* stream);

@@ -62,7 +62,7 @@ def conv2_fwd(a1: torch.Tensor, w: torch.Tensor, b: torch.Tensor, ctrl: torch.Te
     pooled = torch.empty(batch, 12, 12, 64, device="cuda")
     amax = torch.empty(batch, 12, 12, 64, dtype=torch.uint8, device="cuda")
     L = N.lib()
-    fn = L.b200_conv2_fwd_tc2 if tc == 2 else (L.b200_conv2_fwd_tc if tc else L.b200_conv2_fwd_simt)
+    fn = {2: L.b200_conv2_fwd_tc2, 3: L.b200_conv2_fwd_tc3}.get(tc, L.b200_conv2_fwd_tc if tc else L.b200_conv2_fwd_simt)
     N.check(fn(_p(a1), _p(w), _p(b), _p(ctrl), _p(pooled), _p(amax), batch, _s()))
     return pooled, amax
 

@@ -70,7 +70,7 @@ def test_conv1_fwd_gather_normalize(ops, batch):
 
 
 @pytest.mark.parametrize("batch", BATCHES)
-@pytest.mark.parametrize("tc", [False, True, 2])
+@pytest.mark.parametrize("tc", [False, True, 2, 3])
 def test_conv2_fwd_eval(ops, batch, tc):
     _need_tc(tc)
     net = _net()
@@ -89,7 +89,7 @@ def test_conv2_fwd_eval(ops, batch, tc):
     torch.testing.assert_close(picked[live], ref[live], **tol)
 
 
-@pytest.mark.parametrize("tc", [False, True, 2])
+@pytest.mark.parametrize("tc", [False, True, 2, 3])
 def test_conv2_fwd_dropout(ops, tc):
     _need_tc(tc)
     net = _net()
@@ -114,8 +114,9 @@ def test_dropout_masks_identical_simt_vs_tc(ops):
     a1 = torch.rand(16, 26, 26, 32, device="cuda") + 0.1
     c = ops.make_ctrl(train=True, step=11, seed=7)
     s, _ = ops.conv2_fwd(a1, w["conv2.weight"], w["conv2.bias"], c, tc=False)
-    t, _ = ops.conv2_fwd(a1, w["conv2.weight"], w["conv2.bias"], c, tc=True)
-    assert ((s != 0) == (t != 0)).float().mean().item() > 0.9999
+    for variant in (True, 2, 3):
+        t, _ = ops.conv2_fwd(a1, w["conv2.weight"], w["conv2.bias"], c, tc=variant)
+        assert ((s != 0) == (t != 0)).float().mean().item() > 0.9999, variant
 
 
 LAYOUTS = [(False, False), (False, True), (True, True), (True, False)]
