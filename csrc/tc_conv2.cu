@@ -53,7 +53,12 @@ conv2_fwd_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_const
   __shared__ uint32_t tmem_base_smem;
   __shared__ float bias_s[C2];
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // Roles by warp: the TMA producer and the MMA issuer get the two HIGHEST warp ids of the CTA (the warp
+  // arbiter favours high ids, and each then owns an SM sub-partition's top priority); the epilogue warps are
+  // ids 0.. so that id % 4 is their TMEM sub-partition.  `warp` below is the role index (0 producer, 1 MMA,
+  // 2.. epilogue), `wq` the TMEM sub-partition of an epilogue warp.
+  const int warp_id = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5, wq = warp_id & 3;
+  const int warp = warp_id == nwarps - 2 ? 0 : (warp_id == nwarps - 1 ? 1 : warp_id + 2);
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&mapA);
     tma_prefetch_desc(&mapW);
@@ -112,7 +117,7 @@ conv2_fwd_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_const
       }
     }
   } else {
-    const int q = warp & 3;
+    const int q = wq;
     const int train = ctrl->train;
     const unsigned long long seed = ctrl->seed, step = ctrl->step;
     const bool b0 = lane & 1, b3 = (lane >> 3) & 1;
@@ -211,7 +216,12 @@ conv2_dgrad_tc_kernel(const __grid_constant__ CUtensorMap mapDY, const __grid_co
   __shared__ __align__(8) uint64_t full_bar[D_STAGES], empty_bar[D_STAGES], w_bar, tfull_bar[2], tempty_bar[2];
   __shared__ uint32_t tmem_base_smem;
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // Roles by warp: the TMA producer and the MMA issuer get the two HIGHEST warp ids of the CTA (the warp
+  // arbiter favours high ids, and each then owns an SM sub-partition's top priority); the epilogue warps are
+  // ids 0.. so that id % 4 is their TMEM sub-partition.  `warp` below is the role index (0 producer, 1 MMA,
+  // 2.. epilogue), `wq` the TMEM sub-partition of an epilogue warp.
+  const int warp_id = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5, wq = warp_id & 3;
+  const int warp = warp_id == nwarps - 2 ? 0 : (warp_id == nwarps - 1 ? 1 : warp_id + 2);
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&mapDY);
     tma_prefetch_desc(&mapW);
@@ -278,7 +288,7 @@ conv2_dgrad_tc_kernel(const __grid_constant__ CUtensorMap mapDY, const __grid_co
       }
     }
   } else {
-    const int q = warp & 3;
+    const int q = wq;
     const int r = q * 32 + lane;
     const int nl = r / 52, rem = r - nl * 52, hy = rem / 26, x = rem - hy * 26;
     for (int it = 0; it < my_tiles; ++it) {
@@ -327,7 +337,12 @@ conv2_wgrad_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_co
   __shared__ __align__(8) uint64_t full_bar[G_STAGES], empty_bar[G_STAGES], tfull_bar;
   __shared__ uint32_t tmem_base_smem;
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // Roles by warp: the TMA producer and the MMA issuer get the two HIGHEST warp ids of the CTA (the warp
+  // arbiter favours high ids, and each then owns an SM sub-partition's top priority); the epilogue warps are
+  // ids 0.. so that id % 4 is their TMEM sub-partition.  `warp` below is the role index (0 producer, 1 MMA,
+  // 2.. epilogue), `wq` the TMEM sub-partition of an epilogue warp.
+  const int warp_id = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5, wq = warp_id & 3;
+  const int warp = warp_id == nwarps - 2 ? 0 : (warp_id == nwarps - 1 ? 1 : warp_id + 2);
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&mapA1);
     tma_prefetch_desc(&mapDY);
@@ -386,7 +401,7 @@ conv2_wgrad_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_co
       if (leader) umma_commit(&tfull_bar);
     }
   } else {
-    const int q = warp & 3;
+    const int q = wq;
     mbar_wait(&tfull_bar, 0);
     tc_fence_after();
     float* dst = part + (size_t)blockIdx.x * CONV2_PART;
