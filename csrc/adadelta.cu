@@ -52,6 +52,8 @@ adadelta_finalize_kernel(float* __restrict__ p, float* __restrict__ g, float* __
                          int b0_n4, int b1_off, int nchunks, FinalizeSegs segs, B200Ctrl* __restrict__ ctrl, float rho,
                          float eps, int advance, unsigned int* __restrict__ done_counter) {
   __shared__ float4 red[8][64];
+  pdl_trigger();
+  pdl_wait();
   const float lr = ctrl->lr;
   if ((int)blockIdx.x < nchunks) {
     const int col = threadIdx.x & 63, slice = threadIdx.x >> 6, off = blockIdx.x * 256;
@@ -119,8 +121,8 @@ int b200_adadelta_finalize(float* p, float* g, float* v, float* u, long b1_off, 
                            void* ctrl, float rho, float eps, int advance, unsigned int* done_counter, cudaStream_t s) {
   B200_REQUIRE(b1_off % 4 == 0 && nchunks > 0, "adadelta_finalize: bad bucket layout");
   const int grid = nchunks + 2 * b200_sm_count();
-  adadelta_finalize_kernel<<<grid, 512, 0, s>>>(p, g, v, u, (int)(b1_off / 4), (int)b1_off, nchunks, segs,
-                                                (B200Ctrl*)ctrl, rho, eps, advance, done_counter);
+  B200_CHECK(b200_launch(adadelta_finalize_kernel, dim3(grid), dim3(512), 0, s, p, g, v, u, (int)(b1_off / 4),
+                         (int)b1_off, nchunks, segs, (B200Ctrl*)ctrl, rho, eps, advance, done_counter));
   b200_count_launch();
   B200_LAUNCH_CHECK();
   return B200_OK;

@@ -177,6 +177,8 @@ __global__ void __launch_bounds__(512)
 finalize_bucket_kernel(const CommArgs* __restrict__ table, FinalizeSegs segs, float rho, float eps, int advance,
                        unsigned int* __restrict__ done_counter) {
   __shared__ float4 red[8][64];
+  pdl_trigger();
+  pdl_wait();
   const CommArgs& a = table[0];
   const int W = a.world, r = a.rank;
   const uint32_t tok = (uint32_t)(a.ctrl->step) * 2u + 1u;
@@ -349,7 +351,8 @@ int hook_step_end(Engine* E, int advance, cudaStream_t s) {
   if (E->fin_valid) {
     const int chunks = d->plan[1]->n4 / 64;  // the flat layout pads every segment to 256 floats
     B200_REQUIRE(d->plan[1]->n4 % 64 == 0 && chunks <= SYMM_MAX_BLOCKS, "finalize: bucket 1 has %d float4", d->plan[1]->n4);
-    finalize_bucket_kernel<<<chunks, 512, 0, s>>>(d->plan[1]->dev, E->fin, 0.9f, 1e-6f, advance, E->done_counter);
+    B200_CHECK(b200_launch(finalize_bucket_kernel, dim3(chunks), dim3(512), 0, s, (const CommArgs*)d->plan[1]->dev, E->fin,
+                           0.9f, 1e-6f, advance, E->done_counter));
     b200_count_launch();
     B200_LAUNCH_CHECK();
     return B200_OK;

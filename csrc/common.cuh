@@ -31,6 +31,34 @@ void b200_count_launch(int n = 1);
 void b200_launch_reduce_partials(float* dst, const float* src, int n, int nparts, int stride, cudaStream_t s);
 int b200_sm_count();
 
+// ---- programmatic dependent launch (PDL) ---------------------------------------------------------
+// Every kernel of the training step calls pdl_trigger() first (the NEXT kernel of the stream / graph may
+// start being scheduled as soon as all CTAs of this one have started) and pdl_wait() before its first
+// global-memory access (blocks until the PREVIOUS kernel has completed and its writes are visible).
+// Launch latency, block scheduling and the on-chip prologue (barrier init, TMEM allocation) of kernel
+// N+1 thereby overlap the tail of kernel N.  Kernels launched without the attribute behave as before.
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+#endif
+bool b200_pdl_enabled();  // runtime.cu: experimental, only with B200_PDL=1 (see the note there)
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t b200_launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s,
+                               Args&&... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = b200_pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 // ---- model constants (mnist_ddp.py:42-47) -------------------------------------------------
 namespace net {
 constexpr int IMG = 28;

@@ -29,6 +29,8 @@ conv1_fwd_kernel(const uint8_t* __restrict__ images, const int32_t* __restrict__
                  const B200Ctrl* __restrict__ ctrl, const float* __restrict__ w,  // [9][32]
                  const float* __restrict__ bias, float* __restrict__ a1) {       // [B][26][26][32]
   __shared__ float x[IMG * IMG];
+  pdl_trigger();
+  pdl_wait();
   const int b = blockIdx.x;
   const int sample = sample_of(idx, ctrl, b);
   const uint8_t* src = images + (size_t)sample * (IMG * IMG);
@@ -77,6 +79,8 @@ conv1_wgrad_kernel(const uint8_t* __restrict__ images, const int32_t* __restrict
                    float* __restrict__ part) {
   __shared__ float x[IMG * IMG];
   __shared__ float red[8][10][C1];
+  pdl_trigger();
+  pdl_wait();
   // two blocks per image (13 output rows each) so that 2*batch blocks keep every SM busy
   const int b = blockIdx.x >> 1, half = blockIdx.x & 1;
   const int sample = sample_of(idx, ctrl, b);
@@ -152,7 +156,8 @@ void b200_launch_reduce_partials(float* dst, const float* src, int n, int nparts
 extern "C" int b200_conv1_fwd(const uint8_t* images, const int32_t* idx, const void* ctrl, const float* w,
                               const float* bias, float* a1, int batch, void* stream) {
   B200_REQUIRE(batch > 0, "conv1_fwd: batch must be > 0");
-  conv1_fwd_kernel<<<batch, 256, 0, (cudaStream_t)stream>>>(images, idx, (const B200Ctrl*)ctrl, w, bias, a1);
+  B200_CHECK(b200_launch(conv1_fwd_kernel, dim3(batch), dim3(256), 0, (cudaStream_t)stream, images, idx,
+                         (const B200Ctrl*)ctrl, w, bias, a1));
   b200_count_launch();
   B200_LAUNCH_CHECK();
   return B200_OK;
@@ -162,7 +167,7 @@ extern "C" int b200_conv1_wgrad(const uint8_t* images, const int32_t* idx, const
                                 float* part, float* dw, float* db, int batch, void* stream) {
   B200_REQUIRE(batch > 0, "conv1_wgrad: batch must be > 0");
   cudaStream_t s = (cudaStream_t)stream;
-  conv1_wgrad_kernel<<<2 * batch, 256, 0, s>>>(images, idx, (const B200Ctrl*)ctrl, da1, part);
+  B200_CHECK(b200_launch(conv1_wgrad_kernel, dim3(2 * batch), dim3(256), 0, s, images, idx, (const B200Ctrl*)ctrl, da1, part));
   b200_count_launch();
   if (dw) b200_launch_reduce_partials(dw, part, 288, 2 * batch, CONV1_PART, s);  // NULL: caller reduces the partials
   if (db) b200_launch_reduce_partials(db, part + 288, 32, 2 * batch, CONV1_PART, s);

@@ -229,6 +229,8 @@ __global__ void __launch_bounds__(256)
 unpool_dense_kernel(const float* __restrict__ dp, const uint8_t* __restrict__ amax, float* __restrict__ dy, int batch,
                     float* __restrict__ db_part) {
   __shared__ float4 red[256];
+  pdl_trigger();
+  pdl_wait();
   const size_t n4 = (size_t)batch * HP * WP * (C2 / 4);
   float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
   // gridDim.x * 256 is a multiple of 16, so a thread always sees the same channel quad
@@ -322,7 +324,7 @@ extern "C" int b200_unpool_dense(const float* dp, const uint8_t* amax, float* dy
   const size_t n4 = (size_t)batch * HP * WP * (C2 / 4);
   const int grid = (int)min((size_t)(2 * sm_count()), (n4 + 255) / 256);
   cudaStream_t s = (cudaStream_t)stream;
-  unpool_dense_kernel<<<grid, 256, 0, s>>>(dp, amax, dy, batch, db_part);
+  B200_CHECK(b200_launch(unpool_dense_kernel, dim3(grid), dim3(256), 0, s, dp, amax, dy, batch, db_part));
   b200_count_launch();
   if (db) b200_launch_reduce_partials(db, db_part, C2, grid, C2, s);
   B200_LAUNCH_CHECK();

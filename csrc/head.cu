@@ -29,6 +29,8 @@ head_fused_kernel(const float* __restrict__ part, int splits, int batch,      //
 {
   __shared__ float w2s[NCLS][FC1_OUT];
   __shared__ float b2s[NCLS];
+  pdl_trigger();
+  pdl_wait();
   for (int e = threadIdx.x; e < NCLS * FC1_OUT; e += blockDim.x) w2s[e / FC1_OUT][e % FC1_OUT] = w2[e];
   if (threadIdx.x < NCLS) b2s[threadIdx.x] = b2[threadIdx.x];
   __syncthreads();
@@ -124,6 +126,8 @@ head_wgrad_kernel(const float* __restrict__ h, const float* __restrict__ dlogits
                   float* __restrict__ db1, float* __restrict__ loss_out, const B200Ctrl* __restrict__ ctrl,
                   float* __restrict__ loss_ring, int ring, float* __restrict__ loss_ring_host) {
   __shared__ float red[8][FC1_OUT];
+  pdl_trigger();
+  pdl_wait();
   const int j = threadIdx.x & 127, sl = threadIdx.x >> 7;
   const int per = (batch + 7) / 8, b0 = sl * per, b1 = min(batch, b0 + per);
   float s = 0.f;
@@ -180,8 +184,8 @@ extern "C" int b200_head_fused(const float* part, int splits, int batch, const f
                                float* h, float* dlogits, float* dh, float* loss_i, int* correct_i, float* logp,
                                void* stream) {
   B200_REQUIRE(batch > 0 && splits > 0, "head_fused: bad batch/splits");
-  head_fused_kernel<<<ceil_div(batch, 8), 256, 0, (cudaStream_t)stream>>>(
-      part, splits, batch, b1, w2, b2, labels, idx, (const B200Ctrl*)ctrl, h, dlogits, dh, loss_i, correct_i, logp);
+  B200_CHECK(b200_launch(head_fused_kernel, dim3(ceil_div(batch, 8)), dim3(256), 0, (cudaStream_t)stream, part, splits,
+                         batch, b1, w2, b2, labels, idx, (const B200Ctrl*)ctrl, h, dlogits, dh, loss_i, correct_i, logp));
   b200_count_launch();
   B200_LAUNCH_CHECK();
   return B200_OK;
@@ -191,9 +195,8 @@ extern "C" int b200_head_wgrad(const float* h, const float* dlogits, const float
                                int batch, float* dw2, float* db2, float* db1, float* loss_out, const void* ctrl,
                                float* loss_ring, int ring, float* loss_ring_host, void* stream) {
   B200_REQUIRE(batch > 0, "head_wgrad: bad batch");
-  head_wgrad_kernel<<<NCLS + 2, 1024, 0, (cudaStream_t)stream>>>(h, dlogits, dh, loss_i, batch, dw2, db2, db1,
-                                                               loss_out, (const B200Ctrl*)ctrl, loss_ring, ring,
-                                                               loss_ring_host);
+  B200_CHECK(b200_launch(head_wgrad_kernel, dim3(NCLS + 2), dim3(1024), 0, (cudaStream_t)stream, h, dlogits, dh, loss_i,
+                         batch, dw2, db2, db1, loss_out, (const B200Ctrl*)ctrl, loss_ring, ring, loss_ring_host));
   b200_count_launch();
   B200_LAUNCH_CHECK();
   return B200_OK;

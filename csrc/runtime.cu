@@ -1,6 +1,7 @@
 // Process-wide runtime state of libb200mnist: error strings, launch accounting, device facts.
 #include <atomic>
 #include <cstdarg>
+#include <cstdlib>
 #include <cstring>
 
 #include "common.cuh"
@@ -16,6 +17,13 @@ void b200_set_error(const char* fmt, ...) {
 }
 
 void b200_count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+
+bool b200_pdl_enabled() {
+  // Off by default: measured on B200 the early-scheduled dependents cost more (147 vs 137 us/step) than
+  // the hidden launch latency saves, and graph replay was no longer bit-identical to eager launches.
+  static const bool on = getenv("B200_PDL") && atoi(getenv("B200_PDL")) == 1;
+  return on;
+}
 
 int b200_sm_count() {
   static int cached[64] = {0};

@@ -357,6 +357,7 @@ conv2_wgrad_tc2_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_c
   // 2.. epilogue), `wq` the TMEM sub-partition of an epilogue warp.
   const int warp_id = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5, wq = warp_id & 3;
   const int warp = warp_id == nwarps - 2 ? 0 : (warp_id == nwarps - 1 ? 1 : warp_id + 2);
+  pdl_trigger();
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&mapA1);
     tma_prefetch_desc(&mapDY);
@@ -369,6 +370,7 @@ conv2_wgrad_tc2_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_c
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_smem;
+  pdl_wait();
   const int my_items = (nitems - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
 
   if (warp == 0) {
@@ -528,7 +530,7 @@ extern "C" int b200_conv2_wgrad_tc2(const float* dy, const float* a1, float* par
   }
   const int nitems = 3 * batch;
   const int grid = min(nitems, b200_sm_count());
-  conv2_wgrad_tc2_kernel<<<grid, 192, WG_SMEM, s>>>(ma, md, part, nitems);
+  B200_CHECK(b200_launch(conv2_wgrad_tc2_kernel, dim3(grid), dim3(192), (size_t)WG_SMEM, s, ma, md, part, nitems));
   b200_count_launch();
   if (dw) b200_launch_reduce_partials(dw, part, 9 * C2 * C1, grid, CONV2_PART, s);
   B200_LAUNCH_CHECK();

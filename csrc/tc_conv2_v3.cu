@@ -50,6 +50,7 @@ conv2_dgrad_tc3_kernel(const __grid_constant__ CUtensorMap mapDY, const __grid_c
   // 2.. epilogue), `wq` the TMEM sub-partition of an epilogue warp.
   const int warp_id = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5, wq = warp_id & 3;
   const int warp = warp_id == nwarps - 2 ? 0 : (warp_id == nwarps - 1 ? 1 : warp_id + 2);
+  pdl_trigger();
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&mapDY);
     tma_prefetch_desc(&mapW);
@@ -63,6 +64,7 @@ conv2_dgrad_tc3_kernel(const __grid_constant__ CUtensorMap mapDY, const __grid_c
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_smem;
+  pdl_wait();  // on-chip set-up above overlaps the previous kernel's tail
   const int my_items = (nitems - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
 
   if (warp == 0) {
@@ -249,6 +251,7 @@ conv2_fwd_tc3_kernel(const __grid_constant__ CUtensorMap mapP, const __grid_cons
   // 2.. epilogue), `wq` the TMEM sub-partition of an epilogue warp.
   const int warp_id = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5, wq = warp_id & 3;
   const int warp = warp_id == nwarps - 2 ? 0 : (warp_id == nwarps - 1 ? 1 : warp_id + 2);
+  pdl_trigger();
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&mapP);
     tma_prefetch_desc(&mapW);
@@ -259,12 +262,14 @@ conv2_fwd_tc3_kernel(const __grid_constant__ CUtensorMap mapP, const __grid_cons
     }
     fence_barrier_init();
   }
-  if (threadIdx.x < C2) bias_s[threadIdx.x] = bias[threadIdx.x];
   if (warp == 1) tmem_alloc(&tmem_base_smem, 512);  // 2 accumulator slots of 256 columns (192 used)
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_smem;
+  pdl_wait();  // on-chip set-up above overlaps the previous kernel's tail
+  if (threadIdx.x < C2) bias_s[threadIdx.x] = bias[threadIdx.x];
+  __syncthreads();
   const int my_items = (nitems - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
 
   if (warp == 0) {
@@ -399,7 +404,8 @@ extern "C" int b200_conv2_dgrad_tc3(const float* dy, const float* w, const float
   }
   const int nitems = 2 * batch;
   const int grid = min(nitems, b200_sm_count());
-  conv2_dgrad_tc3_kernel<<<grid, 320, DG_SMEM, (cudaStream_t)stream>>>(md, mw, a1, da1, nitems);
+  B200_CHECK(b200_launch(conv2_dgrad_tc3_kernel, dim3(grid), dim3(320), (size_t)DG_SMEM, (cudaStream_t)stream, md, mw, a1,
+                         da1, nitems));
   b200_count_launch();
   B200_LAUNCH_CHECK();
   return B200_OK;
@@ -420,8 +426,8 @@ extern "C" int b200_conv2_fwd_tc3(const float* a1, const float* w, const float* 
   }
   const int nitems = 2 * batch;
   const int grid = min(nitems, b200_sm_count());
-  conv2_fwd_tc3_kernel<<<grid, 320, F3_SMEM, (cudaStream_t)stream>>>(mp, mw, bias, (const B200Ctrl*)ctrl, pooled, amax,
-                                                                    nitems, getenv("B200_DBG") ? atoi(getenv("B200_DBG")) : 0);
+  B200_CHECK(b200_launch(conv2_fwd_tc3_kernel, dim3(grid), dim3(320), (size_t)F3_SMEM, (cudaStream_t)stream, mp, mw, bias,
+                         (const B200Ctrl*)ctrl, pooled, amax, nitems, getenv("B200_DBG") ? atoi(getenv("B200_DBG")) : 0));
   b200_count_launch();
   B200_LAUNCH_CHECK();
   return B200_OK;

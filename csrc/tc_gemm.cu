@@ -86,6 +86,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
   const int kb0 = blockIdx.z * kb_per_split;
   const int nkb = min(kb_per_split, nkb_total - kb0);
 
+  pdl_trigger();
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&mapA);
     tma_prefetch_desc(&mapB);
@@ -98,6 +99,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_smem;
+  pdl_wait();  // everything above is on-chip set-up; global memory is only touched from here on
 
   if (warp == 0) {
     {
@@ -211,7 +213,8 @@ int launch(const CUtensorMap& ma, const CUtensorMap& mb, float* D, int M, int N,
     attr = true;
   }
   dim3 grid(ceil_div(N, BN), ceil_div(M, BM), splits);
-  tc_gemm_kernel<BN, A_MN, B_MN, EPI><<<grid, 192, smem, s>>>(ma, mb, D, M, N, nkb, kbs, aux, scale);
+  B200_CHECK(b200_launch(tc_gemm_kernel<BN, A_MN, B_MN, EPI>, grid, dim3(192), (size_t)smem, s, ma, mb, D, M, N, nkb, kbs,
+                         aux, scale));
   b200_count_launch();
   B200_LAUNCH_CHECK();
   return B200_OK;
