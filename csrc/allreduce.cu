@@ -98,7 +98,7 @@ __device__ __forceinline__ void comm_barrier(const CommArgs& a, int phase, uint3
 template <int MODE, bool OPT>
 __global__ void __launch_bounds__(512, 2)
 fused_allreduce_kernel(const CommArgs* __restrict__ table, uint32_t token, float rho, float eps, int advance,
-                       unsigned int* __restrict__ done_counter) {
+                       unsigned int* __restrict__ done_counter, int exit_barrier) {
   const CommArgs& a = table[blockIdx.y];
   const int W = a.world, r = a.rank;
   const uint32_t tok = token ? token : (uint32_t)(a.ctrl->step) * 2u + 1u;
@@ -156,7 +156,11 @@ fused_allreduce_kernel(const CommArgs* __restrict__ table, uint32_t token, float
     }
   }
   if (MODE == 2) __threadfence_system();  // multimem stores must be performed before the exit signal
-  comm_barrier(a, 1, tok + 1u);
+  // Inside the training step the exit barrier is redundant: the step's two communication kernels
+  // alternate, and the ENTRY barrier of the next one (which every rank reaches only after this kernel
+  // has completed on it) already proves that all peers are done reading / writing.  Stand-alone use
+  // (microbenchmark, tests) keeps it.
+  if (exit_barrier) comm_barrier(a, 1, tok + 1u);
   if (advance >= 0 && threadIdx.x == 0) {
     __threadfence();
     if (atomicAdd(done_counter, 1u) == gridDim.x - 1) {  // every CTA has read ctrl->step / lr by now
@@ -175,7 +179,7 @@ fused_allreduce_kernel(const CommArgs* __restrict__ table, uint32_t token, float
 // partial slices (fixed combination order: deterministic).
 __global__ void __launch_bounds__(512)
 finalize_bucket_kernel(const CommArgs* __restrict__ table, FinalizeSegs segs, float rho, float eps, int advance,
-                       unsigned int* __restrict__ done_counter) {
+                       unsigned int* __restrict__ done_counter, int exit_barrier) {
   __shared__ float4 red[8][64];
   pdl_trigger();
   pdl_wait();
@@ -230,7 +234,7 @@ finalize_bucket_kernel(const CommArgs* __restrict__ table, FinalizeSegs segs, fl
     *reinterpret_cast<float4*>(a.u + i4) = uu;
     *reinterpret_cast<float4*>(a.param[r] + i4) = p;
   }
-  comm_barrier(a, 1, tok + 1u);
+  if (exit_barrier) comm_barrier(a, 1, tok + 1u);  // see fused_allreduce_kernel
   if (advance >= 0 && threadIdx.x == 0) {
     __threadfence();
     if (atomicAdd(done_counter, 1u) == gridDim.x - 1) {
@@ -297,22 +301,23 @@ int default_blocks(const CommPlan* p, int mode) {
 }
 
 int run_plan(const CommPlan* p, int mode, int opt, uint32_t token, int nblocks, float rho, float eps, cudaStream_t s,
-             int advance = -1, unsigned int* done_counter = nullptr) {
+             int advance = -1, unsigned int* done_counter = nullptr, int exit_barrier = 1, int threads = 512) {
   B200_REQUIRE(p && mode >= 0 && mode <= 2, "comm run: bad plan/mode");
   B200_REQUIRE(mode != 2 || p->has_mc, "comm run: NVLS mode needs an arena with a multicast mapping");
   if (nblocks <= 0) nblocks = default_blocks(p, mode);
   B200_REQUIRE(nblocks <= SYMM_MAX_BLOCKS, "comm run: at most %d CTAs", SYMM_MAX_BLOCKS);
   dim3 grid(nblocks, p->slots);
   const CommArgs* tab = p->dev;
-  void* args[] = {(void*)&tab, (void*)&token, (void*)&rho, (void*)&eps, (void*)&advance, (void*)&done_counter};
+  void* args[] = {(void*)&tab, (void*)&token, (void*)&rho, (void*)&eps, (void*)&advance, (void*)&done_counter,
+                  (void*)&exit_barrier};
   const void* fn = mode == 0 ? (opt ? (const void*)fused_allreduce_kernel<0, true> : (const void*)fused_allreduce_kernel<0, false>)
                  : mode == 1 ? (opt ? (const void*)fused_allreduce_kernel<1, true> : (const void*)fused_allreduce_kernel<1, false>)
                              : (opt ? (const void*)fused_allreduce_kernel<2, true> : (const void*)fused_allreduce_kernel<2, false>);
   if (p->slots > 1) {
     // emulated ranks wait on each other inside one launch: all CTAs must be co-resident
-    B200_CHECK(cudaLaunchCooperativeKernel(fn, grid, dim3(512), args, 0, s));
+    B200_CHECK(cudaLaunchCooperativeKernel(fn, grid, dim3(threads), args, 0, s));
   } else {
-    B200_CHECK(cudaLaunchKernel(fn, grid, dim3(512), args, 0, s));
+    B200_CHECK(cudaLaunchKernel(fn, grid, dim3(threads), args, 0, s));
   }
   b200_count_launch();
   return B200_OK;
@@ -329,12 +334,17 @@ struct DdpState {
 int hook_bucket_ready(Engine* E, int bucket, cudaStream_t s) {
   DdpState* d = (DdpState*)E->hooks.state;
   static const bool no_side = getenv("B200_DDP_NO_SIDE") != nullptr;  // diagnostics: serialise bucket 0
-  if (bucket == 0 && no_side) return run_plan(d->plan[0], d->mode[0], 1, 0, 0, 0.9f, 1e-6f, s);
+  static const int exit_b = getenv("B200_DDP_EXIT_BARRIER") ? atoi(getenv("B200_DDP_EXIT_BARRIER")) : 0;
+  if (bucket == 0 && no_side) return run_plan(d->plan[0], d->mode[0], 1, 0, 0, 0.9f, 1e-6f, s, -1, nullptr, exit_b);
   if (bucket == 0) {
     // fc buckets are complete while the conv backward still runs: reduce them on a side stream
     B200_CHECK(cudaEventRecord(d->fork, s));
     B200_CHECK(cudaStreamWaitEvent(d->comm, d->fork, 0));
-    int r = run_plan(d->plan[0], d->mode[0], 1, 0, 0, 0.9f, 1e-6f, d->comm);
+    // Footprint of the side-stream reducer (env-tunable).  Measured at W = 2 (us/step): 64x512 160.8,
+    // 37x512 167, 148x512 174, 74x256 172, 148x256 186, 148x128 206 — few fat CTAs beat one light CTA per SM.
+    static const int nb0 = getenv("B200_DDP_B0_BLOCKS") ? atoi(getenv("B200_DDP_B0_BLOCKS")) : 64;
+    static const int th0 = getenv("B200_DDP_B0_THREADS") ? atoi(getenv("B200_DDP_B0_THREADS")) : 512;
+    int r = run_plan(d->plan[0], d->mode[0], 1, 0, min(nb0, SYMM_MAX_BLOCKS), 0.9f, 1e-6f, d->comm, -1, nullptr, exit_b, th0);
     if (r != B200_OK) return r;
     B200_CHECK(cudaEventRecord(d->join, d->comm));
     return B200_OK;
@@ -351,8 +361,9 @@ int hook_step_end(Engine* E, int advance, cudaStream_t s) {
   if (E->fin_valid) {
     const int chunks = d->plan[1]->n4 / 64;  // the flat layout pads every segment to 256 floats
     B200_REQUIRE(d->plan[1]->n4 % 64 == 0 && chunks <= SYMM_MAX_BLOCKS, "finalize: bucket 1 has %d float4", d->plan[1]->n4);
+    static const int exit_b = getenv("B200_DDP_EXIT_BARRIER") ? atoi(getenv("B200_DDP_EXIT_BARRIER")) : 0;
     B200_CHECK(b200_launch(finalize_bucket_kernel, dim3(chunks), dim3(512), 0, s, (const CommArgs*)d->plan[1]->dev, E->fin,
-                           0.9f, 1e-6f, advance, E->done_counter));
+                           0.9f, 1e-6f, advance, E->done_counter, exit_b));
     b200_count_launch();
     B200_LAUNCH_CHECK();
     return B200_OK;
