@@ -68,13 +68,15 @@ template <int BN, bool A_MN, bool B_MN, int EPI>
 __global__ void __launch_bounds__(192, 1)
 tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
                float* __restrict__ D, int M, int N, int nkb_total, int kb_per_split, const float* __restrict__ aux,
-               float scale) {
+               float scale, const uint8_t* __restrict__ amax, float* __restrict__ dy, float* __restrict__ db_part) {
   constexpr int B_BYTES = BN * BK * 4;
   constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);  // SW128 needs 1 KiB alignment
   __shared__ __align__(8) uint64_t full_bar[STAGES], empty_bar[STAGES], tmem_full_bar;
   __shared__ uint32_t tmem_base_smem;
+  __shared__ float tr_s[EPI == 2 ? 4 : 1][EPI == 2 ? 32 : 1][33];  // EPI 2: per-warp transpose tile (row -> channel owner)
+  __shared__ float cs_s[EPI == 2 ? 4 : 1][EPI == 2 ? BN : 1];       //        per-warp column sums of the CTA tile
 
   // Roles by warp: the TMA producer and the MMA issuer get the two HIGHEST warp ids of the CTA (the warp
   // arbiter favours high ids, and each then owns an SM sub-partition's top priority); the epilogue warps are
@@ -149,7 +151,37 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
     for (int c0 = 0; c0 < BN; c0 += 32) {
       float v[32];
       tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + c0, v);
-      if (m < M) {
+      if (EPI == 2) {
+        // fc1 dgrad fused with the dropout/ReLU mask, the max-pool scatter and conv2's bias gradient.
+        // Columns n0+c0 .. +31 are 32 consecutive channels of ONE pooled pixel.  The chunk is transposed
+        // through shared memory so that a lane owns a CHANNEL and walks the warp's 32 samples: every
+        // global access below is then one fully coalesced 128-byte (or 32-byte) line per warp, and the
+        // per-channel sum for the bias gradient falls out of the same loop.
+        const int n = n0 + c0;
+#pragma unroll
+        for (int j = 0; j < 32; ++j) tr_s[q][lane][j] = v[j];
+        __syncwarp();
+        float cs = 0.f;
+        if (n < N) {
+          const int hw = n >> 6, cb = (n & 63) + lane, ph = hw / 12, pw = hw - ph * 12;
+          const int rows = min(32, M - (m0 + q * 32));
+#pragma unroll 4
+          for (int r = 0; r < rows; ++r) {
+            const size_t mr = (size_t)(m0 + q * 32 + r);
+            const float pv = aux[mr * N + n + lane];
+            const uint32_t am = amax[mr * N + n + lane];
+            const float val = pv > 0.f ? tr_s[q][r][lane] * scale : 0.f;
+            cs += val;
+            float* dst = dy + ((mr * 24 + 2 * ph) * 24 + 2 * pw) * 64 + cb;
+            dst[0] = am == 0u ? val : 0.f;
+            dst[64] = am == 1u ? val : 0.f;
+            dst[24 * 64] = am == 2u ? val : 0.f;
+            dst[24 * 64 + 64] = am == 3u ? val : 0.f;
+          }
+        }
+        cs_s[q][c0 + lane] = cs;
+        __syncwarp();
+      } else if (m < M) {
 #pragma unroll
         for (int j = 0; j < 32; j += 4) {
           const int n = n0 + c0 + j;
@@ -164,6 +196,12 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
           }
         }
       }
+    }
+    if (EPI == 2) {
+      asm volatile("bar.sync 1, 128;" ::: "memory");  // the four epilogue warps only
+      const int t = q * 32 + lane;                      // 0..127
+      if (t < BN && n0 + t < N)
+        db_part[(size_t)blockIdx.y * N + n0 + t] = (cs_s[0][t] + cs_s[1][t]) + (cs_s[2][t] + cs_s[3][t]);
     }
   }
   tc_fence_before();
@@ -205,7 +243,8 @@ int get_map(const float* p, int R, int K, int mn, int tile, CUtensorMap* out) {
 
 template <int BN, bool A_MN, bool B_MN, int EPI>
 int launch(const CUtensorMap& ma, const CUtensorMap& mb, float* D, int M, int N, int nkb, int kbs, int splits,
-           const float* aux, float scale, cudaStream_t s) {
+           const float* aux, float scale, cudaStream_t s, const uint8_t* amax = nullptr, float* dy = nullptr,
+           float* db_part = nullptr) {
   constexpr int smem = STAGES * (A_BYTES + BN * BK * 4) + 1024;
   static bool attr = false;
   if (!attr) {
@@ -214,7 +253,7 @@ int launch(const CUtensorMap& ma, const CUtensorMap& mb, float* D, int M, int N,
   }
   dim3 grid(ceil_div(N, BN), ceil_div(M, BM), splits);
   B200_CHECK(b200_launch(tc_gemm_kernel<BN, A_MN, B_MN, EPI>, grid, dim3(192), (size_t)smem, s, ma, mb, D, M, N, nkb, kbs,
-                         aux, scale));
+                         aux, scale, amax, dy, db_part));
   b200_count_launch();
   B200_LAUNCH_CHECK();
   return B200_OK;
@@ -258,4 +297,20 @@ extern "C" int b200_tc_gemm(const float* A, const float* B, float* D, int M, int
   }
   return epi ? dispatch_major<64, 1>(a_mn, b_mn, ma, mb, D, M, N, nkb, kbs, splits, aux, scale, s)
              : dispatch_major<64, 0>(a_mn, b_mn, ma, mb, D, M, N, nkb, kbs, splits, aux, scale, s);
+}
+
+// fc1 dgrad + dropout/ReLU mask + max-pool scatter + conv2 bias-gradient partials in one tcgen05 GEMM:
+//   dY[B][24][24][64]  <-  (dh[B][128] . W1[128][9216]) * (pooled > 0 ? scale : 0), routed by amax
+//   db_part[ceil(B/128)][9216] = per-CTA column sums (conv2.bias grad = sum over parts and over the 144 pixels)
+extern "C" int b200_fc1_dgrad_unpool_tc(const float* dh, const float* w1, const float* pooled, const uint8_t* amax,
+                                        float* dy, float* db_part, int batch, float scale, void* stream) {
+  B200_REQUIRE(batch > 0 && dh && w1 && pooled && amax && dy && db_part, "fc1_dgrad_unpool_tc: bad arguments");
+  const int M = batch, N = 9216, K = 128;
+  CUtensorMap ma, mb;
+  int r = get_map(dh, M, K, 0, BM, &ma);
+  if (r != B200_OK) return r;
+  r = get_map(w1, N, K, 1, 128, &mb);
+  if (r != B200_OK) return r;
+  return launch<128, false, true, 2>(ma, mb, nullptr, M, N, ceil_div(K, BK), ceil_div(K, BK), 1, pooled, scale,
+                                     (cudaStream_t)stream, amax, dy, db_part);
 }

@@ -79,6 +79,10 @@ int b200_sgemm(const float* A, long sam, long sak, const float* B, long sbk, lon
  * Host-side set-up (tensor maps) is cached per (pointer, shape). */
 int b200_tc_gemm(const float* A, const float* B, float* D, int M, int N, int K, int a_mn, int b_mn, int splits,
                  int epi, const float* aux, float scale, void* stream);
+/* fc1 dgrad fused with the dropout/ReLU mask, the max-pool scatter (writes the dense dY directly) and
+ * per-CTA partial sums of conv2's bias gradient: db_part[ceil(batch/128)][9216] */
+int b200_fc1_dgrad_unpool_tc(const float* dh, const float* w1, const float* pooled, const uint8_t* amax, float* dy,
+                             float* db_part, int batch, float scale, void* stream);
 /* implicit-GEMM conv2 forward with the fused bias+ReLU+pool+dropout epilogue (same outputs as _simt) */
 int b200_conv2_fwd_tc(const float* a1, const float* w, const float* bias, const void* ctrl, float* pooled,
                       uint8_t* amax, int batch, void* stream);

@@ -119,6 +119,7 @@ _SIGNATURES = {
     "b200_unpool_dense": [_vp, _vp, _vp, _vp, _vp, _i, _vp],
     "b200_sgemm": [_vp, _l, _l, _vp, _l, _l, _vp, _i, _i, _i, _i, _i, _vp, _f, _vp],
     "b200_tc_gemm": [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp, _f, _vp],
+    "b200_fc1_dgrad_unpool_tc": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _f, _vp],
     "b200_conv2_fwd_tc": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _vp],
     "b200_conv2_fwd_tc2": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _vp],
     "b200_conv2_dgrad_tc2": [_vp, _vp, _vp, _vp, _i, _vp],

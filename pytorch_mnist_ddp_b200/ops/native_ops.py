@@ -80,6 +80,16 @@ def unpool_dense(dp: torch.Tensor, amax: torch.Tensor, with_db: bool = False):
     return dy, db
 
 
+def fc1_dgrad_unpool(dh: torch.Tensor, w1: torch.Tensor, pooled: torch.Tensor, amax: torch.Tensor, scale: float):
+    """Fused fc1 dgrad + mask + un-pool: returns (dY [B,24,24,64], conv2 bias gradient [64])."""
+    batch = dh.shape[0]
+    mt = (batch + 127) // 128
+    dy = torch.empty(batch, 24, 24, 64, device="cuda")
+    part = torch.empty(mt, 9216, device="cuda")
+    N.check(N.lib().b200_fc1_dgrad_unpool_tc(_p(dh), _p(w1), _p(pooled), _p(amax), _p(dy), _p(part), batch, scale, _s()))
+    return dy, part.view(mt * 144, 64).sum(0)
+
+
 def conv2_dgrad(dp, amax, w, a1, tc: bool = False) -> torch.Tensor:
     batch = dp.shape[0]
     da1 = torch.empty(batch, 26, 26, 32, device="cuda")

@@ -269,3 +269,20 @@ def test_adadelta_advances_ctrl(ops):
     ops.adadelta(p, g, v, u, ctrl, advance=200)
     c = ops.read_ctrl(ctrl)
     assert c["step"] == 6 and c["pos"] == 300
+
+
+@pytest.mark.parametrize("batch", [7, 64, 200, 300])
+def test_fc1_dgrad_fused_with_unpool(ops, batch):
+    _need_tc(True)
+    dh = torch.randn(batch, 128, device="cuda") * 0.1
+    w1 = torch.randn(128, 9216, device="cuda") * 0.05
+    pooled = torch.randn(batch, 12, 12, 64, device="cuda").clamp_min(0)
+    amax = torch.randint(0, 4, (batch, 12, 12, 64), dtype=torch.uint8, device="cuda")
+    dy, db = ops.fc1_dgrad_unpool(dh, w1, pooled, amax, 1 / 0.75)
+    dp = (dh @ w1).view(batch, 12, 12, 64) * (pooled > 0) / 0.75
+    ref = torch.zeros(batch, 24, 24, 64, device="cuda")
+    for s in range(4):
+        ref[:, (s >> 1)::2, (s & 1)::2, :] = dp * (amax == s)
+    torch.testing.assert_close(dy, ref, rtol=2e-2, atol=2e-2)
+    assert ((dy != 0).sum(dim=(1, 2)) <= 144).all()  # at most one non-zero per pooling window and channel
+    torch.testing.assert_close(db, dp.sum(dim=(0, 1, 2)), rtol=2e-2, atol=5e-2)
