@@ -204,3 +204,31 @@ def test_checkpoint_roundtrip_through_reference_format(tmp_path):
         ref = net(_norm(test.images[:32]).cuda())
     torch.testing.assert_close(eng.forward_logp(1, 0, 32), ref, rtol=1e-3, atol=1e-3)
     eng.close()
+
+
+def test_cli_runs_on_the_native_engine(tmp_path):
+    """mnist.py / mnist_ddp.py on a GPU: native backend, reference log formats, reference checkpoint names."""
+    import os
+    import re
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    from pytorch_mnist_ddp_b200.utils import data
+    data.write_idx_files(str(tmp_path / "data"), data.synthetic_split(True, 2048), data.synthetic_split(False, 512))
+    env = dict(os.environ, PYTHONPATH=root)
+    for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK"):
+        env.pop(k, None)
+    res = subprocess.run([sys.executable, os.path.join(root, "mnist_ddp.py"), "--epochs", "2", "--batch-size", "200",
+                          "--test-batch-size", "256", "--save-model", "--data-root", str(tmp_path / "data")],
+                         cwd=str(tmp_path), env=env, capture_output=True, text=True, timeout=300)
+    assert res.returncode == 0, res.stderr[-2000:]
+    out = res.stdout
+    assert out.startswith("Not using distributed mode")
+    lines = [l for l in out.splitlines() if l.startswith("Train Epoch")]
+    assert len(lines) == 4 and lines[0].startswith("Train Epoch: 1 [0/2048 (0%)]\tLoss: 2.")  # 11 steps, log every 10
+    # the reference prints batch_idx * len(data); batch 10 is the 48-image tail (mnist.py:48-51)
+    assert lines[1].startswith("Train Epoch: 1 [480/2048 (91%)]")
+    assert len(re.findall(r"Test set: Average loss: \d\.\d{4}, Accuracy: \d+/512 \(\d+%\)", out)) == 2
+    assert "Total cost time:" in out
+    sd = torch.load(str(tmp_path / "mnist_cnn_.pt"), weights_only=True)
+    assert list(sd)[0] == "conv1.weight" and sd["fc1.weight"].shape == (128, 9216)
