@@ -47,11 +47,11 @@ adadelta_kernel(float* __restrict__ p, const float* __restrict__ g, float* __res
 // CTAs [0, nchunks) each own 256 floats of the conv bucket (reduce partials in a fixed order, then
 // Adadelta); the remaining CTAs stream over the fc bucket.  Replaces four reduction launches plus the
 // plain Adadelta launch.
-__global__ void __launch_bounds__(512)
+__global__ void __launch_bounds__(1024)
 adadelta_finalize_kernel(float* __restrict__ p, float* __restrict__ g, float* __restrict__ v, float* __restrict__ u,
                          int b0_n4, int b1_off, int nchunks, FinalizeSegs segs, B200Ctrl* __restrict__ ctrl, float rho,
                          float eps, int advance, unsigned int* __restrict__ done_counter) {
-  __shared__ float4 red[8][64];
+  __shared__ float4 red[FIN_SLICES][64];
   pdl_trigger();
   pdl_wait();
   const float lr = ctrl->lr;
@@ -64,7 +64,7 @@ adadelta_finalize_kernel(float* __restrict__ p, float* __restrict__ g, float* __
       const int e = off - sg.dst_off + 4 * col;
       if (sg.src && e >= 0 && e < sg.n) {
 #pragma unroll 8
-        for (int q = slice; q < sg.nparts; q += 8) {
+        for (int q = slice; q < sg.nparts; q += FIN_SLICES) {
           const float4 x = *reinterpret_cast<const float4*>(sg.src + (size_t)q * sg.stride + e);
           acc.x += x.x; acc.y += x.y; acc.z += x.z; acc.w += x.w;
         }
@@ -75,7 +75,7 @@ adadelta_finalize_kernel(float* __restrict__ p, float* __restrict__ g, float* __
     if (slice == 0) {
       float4 t = red[0][col];
 #pragma unroll
-      for (int q = 1; q < 8; ++q) { const float4 x = red[q][col]; t.x += x.x; t.y += x.y; t.z += x.z; t.w += x.w; }
+      for (int q = 1; q < FIN_SLICES; ++q) { const float4 x = red[q][col]; t.x += x.x; t.y += x.y; t.z += x.z; t.w += x.w; }
       const size_t i = (size_t)b1_off + off + 4 * col;
       *reinterpret_cast<float4*>(g + i) = t;  // keep the gradient buffer complete (tests, debugging)
       float4 pp = *reinterpret_cast<float4*>(p + i), vv = *reinterpret_cast<float4*>(v + i),
@@ -118,10 +118,13 @@ adadelta_finalize_kernel(float* __restrict__ p, float* __restrict__ g, float* __
 
 // bucket 0 = floats [0, b1_off) (fc), bucket 1 = floats [b1_off, b1_off + 256*nchunks) (conv, as partials)
 int b200_adadelta_finalize(float* p, float* g, float* v, float* u, long b1_off, int nchunks, const FinalizeSegs& segs,
-                           void* ctrl, float rho, float eps, int advance, unsigned int* done_counter, cudaStream_t s) {
+                           void* ctrl, float rho, float eps, int advance, unsigned int* done_counter,
+                           bool bucket0_done, cudaStream_t s) {
   B200_REQUIRE(b1_off % 4 == 0 && nchunks > 0, "adadelta_finalize: bad bucket layout");
-  const int grid = nchunks + 2 * b200_sm_count();
-  B200_CHECK(b200_launch(adadelta_finalize_kernel, dim3(grid), dim3(512), 0, s, p, g, v, u, (int)(b1_off / 4),
+  // bucket0_done: the fc bucket was already updated elsewhere (engine branch stream); only the conv chunks run
+  const int grid = nchunks + (bucket0_done ? 0 : 2 * b200_sm_count());
+  B200_CHECK(b200_launch(adadelta_finalize_kernel, dim3(grid), dim3(64 * FIN_SLICES), 0, s, p, g, v, u,
+                         bucket0_done ? 0 : (int)(b1_off / 4),
                          (int)b1_off, nchunks, segs, (B200Ctrl*)ctrl, rho, eps, advance, done_counter));
   b200_count_launch();
   B200_LAUNCH_CHECK();
@@ -135,8 +138,8 @@ extern "C" int b200_adadelta(float* p, const float* g, float* v, float* u, long 
   B200_REQUIRE(n > 0 && n % 4 == 0, "adadelta: n (%ld) must be a positive multiple of 4", n);
   const int n4 = (int)(n / 4);
   const int grid = min(ceil_div(n4, 256), 4 * b200_sm_count());
-  adadelta_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(p, g, v, u, n4, (B200Ctrl*)ctrl, rho, eps, advance_batch,
-                                                         done_counter);
+  B200_CHECK(b200_launch(adadelta_kernel, dim3(grid), dim3(256), 0, (cudaStream_t)stream, p, g, v, u, n4, (B200Ctrl*)ctrl,
+                         rho, eps, advance_batch, done_counter));
   b200_count_launch();
   B200_LAUNCH_CHECK();
   return B200_OK;

@@ -175,12 +175,12 @@ fused_allreduce_kernel(const CommArgs* __restrict__ table, uint32_t token, float
 // The conv bucket's last kernel: (1) reduce the per-CTA partial sums that the wgrad kernels left behind
 // into this rank's gradient bucket, (2) one-shot all-reduce across ranks, (3) 1/W + Adadelta, (4) end
 // of step.  One CTA owns 256 consecutive floats of the bucket from start to finish, so the only
-// cross-CTA ordering needed is the per-CTA cross-GPU barrier.  512 threads = 64 float4 columns x 8
+// cross-CTA ordering needed is the per-CTA cross-GPU barrier.  1024 threads = 64 float4 columns x 16
 // partial slices (fixed combination order: deterministic).
-__global__ void __launch_bounds__(512)
+__global__ void __launch_bounds__(1024)
 finalize_bucket_kernel(const CommArgs* __restrict__ table, FinalizeSegs segs, float rho, float eps, int advance,
                        unsigned int* __restrict__ done_counter, int exit_barrier) {
-  __shared__ float4 red[8][64];
+  __shared__ float4 red[FIN_SLICES][64];
   pdl_trigger();
   pdl_wait();
   const CommArgs& a = table[0];
@@ -196,7 +196,7 @@ finalize_bucket_kernel(const CommArgs* __restrict__ table, FinalizeSegs segs, fl
     const int e = off - sg.dst_off + 4 * col;
     if (sg.src && e >= 0 && e < sg.n) {
 #pragma unroll 8
-      for (int p = slice; p < sg.nparts; p += 8) {
+      for (int p = slice; p < sg.nparts; p += FIN_SLICES) {
         const float4 v = *reinterpret_cast<const float4*>(sg.src + (size_t)p * sg.stride + e);
         acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
       }
@@ -208,7 +208,7 @@ finalize_bucket_kernel(const CommArgs* __restrict__ table, FinalizeSegs segs, fl
   if (slice == 0) {
     float4 t = red[0][col];
 #pragma unroll
-    for (int q = 1; q < 8; ++q) { const float4 v = red[q][col]; t.x += v.x; t.y += v.y; t.z += v.z; t.w += v.w; }
+    for (int q = 1; q < FIN_SLICES; ++q) { const float4 v = red[q][col]; t.x += v.x; t.y += v.y; t.z += v.z; t.w += v.w; }
     *reinterpret_cast<float4*>(mygrad) = t;
   }
   comm_barrier(a, 0, tok);  // release is cumulative over the gradient stores above
@@ -313,6 +313,7 @@ int run_plan(const CommPlan* p, int mode, int opt, uint32_t token, int nblocks, 
   const void* fn = mode == 0 ? (opt ? (const void*)fused_allreduce_kernel<0, true> : (const void*)fused_allreduce_kernel<0, false>)
                  : mode == 1 ? (opt ? (const void*)fused_allreduce_kernel<1, true> : (const void*)fused_allreduce_kernel<1, false>)
                              : (opt ? (const void*)fused_allreduce_kernel<2, true> : (const void*)fused_allreduce_kernel<2, false>);
+  b200_prefer_max_shared(fn);  // so the side-stream reducer can share SMs with the persistent conv CTAs
   if (p->slots > 1) {
     // emulated ranks wait on each other inside one launch: all CTAs must be co-resident
     B200_CHECK(cudaLaunchCooperativeKernel(fn, grid, dim3(threads), args, 0, s));
@@ -362,7 +363,7 @@ int hook_step_end(Engine* E, int advance, cudaStream_t s) {
     const int chunks = d->plan[1]->n4 / 64;  // the flat layout pads every segment to 256 floats
     B200_REQUIRE(d->plan[1]->n4 % 64 == 0 && chunks <= SYMM_MAX_BLOCKS, "finalize: bucket 1 has %d float4", d->plan[1]->n4);
     static const int exit_b = getenv("B200_DDP_EXIT_BARRIER") ? atoi(getenv("B200_DDP_EXIT_BARRIER")) : 0;
-    B200_CHECK(b200_launch(finalize_bucket_kernel, dim3(chunks), dim3(512), 0, s, (const CommArgs*)d->plan[1]->dev, E->fin,
+    B200_CHECK(b200_launch(finalize_bucket_kernel, dim3(chunks), dim3(64 * FIN_SLICES), 0, s, (const CommArgs*)d->plan[1]->dev, E->fin,
                            0.9f, 1e-6f, advance, E->done_counter, exit_b));
     b200_count_launch();
     B200_LAUNCH_CHECK();

@@ -43,9 +43,16 @@ __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;"
 #endif
 bool b200_pdl_enabled();  // runtime.cu: experimental, only with B200_PDL=1 (see the note there)
 
+// Every kernel of the step asks for the maximum shared-memory carve-out, also those that use little or
+// no shared memory.  An SM only runs CTAs of kernels with the same L1/shared split at the same time, and
+// the persistent tcgen05 kernels need (nearly) all 228 KB: with the default preference a small kernel on
+// a branch stream would wait for those CTAs to drain instead of running beside them (measured).
+void b200_prefer_max_shared(const void* kernel);  // runtime.cu; once per kernel
+
 template <typename... KArgs, typename... Args>
 inline cudaError_t b200_launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s,
                                Args&&... args) {
+  b200_prefer_max_shared((const void*)kernel);
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = grid;
   cfg.blockDim = block;
@@ -58,6 +65,48 @@ inline cudaError_t b200_launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, 
   cfg.numAttrs = b200_pdl_enabled() ? 1 : 0;
   return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
+
+// ---- second-level reduction of per-CTA partial rows, inside the producing kernel ---------------------
+// Kernels that leave one partial row per CTA (conv1 wgrad: 2*batch rows, un-pool: ~300 rows) call this
+// at their end: of every GROUP_ROWS consecutive CTAs the one that finishes last adds the group's rows
+// (fixed order, so still deterministic) into gpart[group].  The step's final kernel then has ~8x fewer
+// rows to walk through, which is what its latency is made of.  counters: one zero-initialised word per
+// group; the combining CTA resets it, so the kernel can be replayed from a graph.
+#ifdef __CUDACC__
+constexpr int GROUP_ROWS = 8;
+__device__ __forceinline__ void group_reduce_rows(const float* part, int stride, int n, float* gpart,
+                                                  unsigned int* counters) {
+  __shared__ int s_last;
+  const int grp = blockIdx.x / GROUP_ROWS;
+  const int gsize = min(GROUP_ROWS, (int)gridDim.x - grp * GROUP_ROWS);
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned int prev = atomicAdd(&counters[grp], 1u);
+    s_last = prev == (unsigned int)(gsize - 1);
+    if (s_last) counters[grp] = 0;
+  }
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  const float* src = part + (size_t)grp * GROUP_ROWS * stride;
+  for (int e = threadIdx.x; e < n; e += blockDim.x) {
+    float v[GROUP_ROWS];
+#pragma unroll
+    for (int q = 0; q < GROUP_ROWS; ++q) v[q] = q < gsize ? __ldcg(src + (size_t)q * stride + e) : 0.f;
+    float s = v[0];
+#pragma unroll
+    for (int q = 1; q < GROUP_ROWS; ++q) s += v[q];
+    gpart[(size_t)grp * stride + e] = s;
+  }
+}
+#endif
+// engine-internal variants of b200_conv1_wgrad / b200_unpool_dense that also combine groups of partial rows
+int b200_conv1_wgrad_grouped(const uint8_t* images, const int32_t* idx, const void* ctrl, const float* da1, float* part,
+                             float* gpart, unsigned int* counters, int batch, cudaStream_t s);
+int b200_unpool_dense_grouped(const float* dp, const uint8_t* amax, float* dy, float* db_part, float* db_gpart,
+                              unsigned int* counters, int batch, cudaStream_t s);
+inline int b200_group_count(int rows) { return (rows + 7) / 8; }
 
 // ---- model constants (mnist_ddp.py:42-47) -------------------------------------------------
 namespace net {

@@ -76,9 +76,13 @@ constexpr int CONV1_PART = 320;
 __global__ void __launch_bounds__(256)
 conv1_wgrad_kernel(const uint8_t* __restrict__ images, const int32_t* __restrict__ idx,
                    const B200Ctrl* __restrict__ ctrl, const float* __restrict__ da1,  // [B][26][26][32]
-                   float* __restrict__ part) {
-  __shared__ float x[IMG * IMG];
-  __shared__ float red[8][10][C1];
+                   float* __restrict__ part, float* __restrict__ gpart = nullptr,
+                   unsigned int* __restrict__ counters = nullptr) {
+  // x (the image) and red (the cross-warp reduction) share storage: 10 KB of static shared memory lets
+  // these CTAs co-reside with a conv2 wgrad CTA (214 KB) that runs on the engine's branch stream
+  __shared__ __align__(16) float sh[8 * 10 * C1];
+  float* x = sh;
+  float (*red)[10][C1] = reinterpret_cast<float (*)[10][C1]>(sh);
   pdl_trigger();
   pdl_wait();
   // two blocks per image (13 output rows each) so that 2*batch blocks keep every SM busy
@@ -115,6 +119,7 @@ conv1_wgrad_kernel(const uint8_t* __restrict__ images, const int32_t* __restrict
       acc[9] += d[u];
     }
   }
+  __syncthreads();  // everybody is done with x
 #pragma unroll
   for (int t = 0; t < 10; ++t) red[g][t][o] = acc[t];
   __syncthreads();
@@ -125,6 +130,7 @@ conv1_wgrad_kernel(const uint8_t* __restrict__ images, const int32_t* __restrict
     for (int gg = 0; gg < 8; ++gg) s += red[gg][t][oo];
     part[(size_t)blockIdx.x * CONV1_PART + e] = s;  // e = t*32+o: taps first (288), then bias (32)
   }
+  if (gpart) group_reduce_rows(part, CONV1_PART, CONV1_PART, gpart, counters);
 }
 
 // dst[e] = sum_{p < nparts} src[p*stride + e]  — fixed order, so results are run-to-run identical.
@@ -167,10 +173,21 @@ extern "C" int b200_conv1_wgrad(const uint8_t* images, const int32_t* idx, const
                                 float* part, float* dw, float* db, int batch, void* stream) {
   B200_REQUIRE(batch > 0, "conv1_wgrad: batch must be > 0");
   cudaStream_t s = (cudaStream_t)stream;
-  B200_CHECK(b200_launch(conv1_wgrad_kernel, dim3(2 * batch), dim3(256), 0, s, images, idx, (const B200Ctrl*)ctrl, da1, part));
+  B200_CHECK(b200_launch(conv1_wgrad_kernel, dim3(2 * batch), dim3(256), 0, s, images, idx, (const B200Ctrl*)ctrl, da1, part,
+                         (float*)nullptr, (unsigned int*)nullptr));
   b200_count_launch();
   if (dw) b200_launch_reduce_partials(dw, part, 288, 2 * batch, CONV1_PART, s);  // NULL: caller reduces the partials
   if (db) b200_launch_reduce_partials(db, part + 288, 32, 2 * batch, CONV1_PART, s);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+int b200_conv1_wgrad_grouped(const uint8_t* images, const int32_t* idx, const void* ctrl, const float* da1, float* part,
+                             float* gpart, unsigned int* counters, int batch, cudaStream_t s) {
+  B200_REQUIRE(batch > 0 && gpart && counters, "conv1_wgrad_grouped: bad arguments");
+  B200_CHECK(b200_launch(conv1_wgrad_kernel, dim3(2 * batch), dim3(256), 0, s, images, idx, (const B200Ctrl*)ctrl, da1, part,
+                         gpart, counters));
+  b200_count_launch();
   B200_LAUNCH_CHECK();
   return B200_OK;
 }
@@ -240,7 +257,7 @@ extern "C" int b200_conv1_wgrad_noalloc(const uint8_t* images, const int32_t* id
   int r = noalloc_scratch_for_current_device(&scratch);
   if (r != B200_OK) return r;
   cudaStream_t s = (cudaStream_t)stream;
-  conv1_wgrad_kernel<<<2 * batch, 256, 0, s>>>(images, idx, (const B200Ctrl*)ctrl, da1, scratch);
+  conv1_wgrad_kernel<<<2 * batch, 256, 0, s>>>(images, idx, (const B200Ctrl*)ctrl, da1, scratch, nullptr, nullptr);
   b200_count_launch();
   b200_launch_reduce_partials(dw, scratch, 288, 2 * batch, CONV1_PART, s);
   b200_launch_reduce_partials(db, scratch + 288, 32, 2 * batch, CONV1_PART, s);

@@ -227,7 +227,7 @@ conv2_wgrad_simt_kernel(const float* __restrict__ dp, const uint8_t* __restrict_
 // is an element of dp) in db_part[block][64].
 __global__ void __launch_bounds__(256)
 unpool_dense_kernel(const float* __restrict__ dp, const uint8_t* __restrict__ amax, float* __restrict__ dy, int batch,
-                    float* __restrict__ db_part) {
+                    float* __restrict__ db_part, float* __restrict__ db_gpart, unsigned int* __restrict__ counters) {
   __shared__ float4 red[256];
   pdl_trigger();
   pdl_wait();
@@ -260,6 +260,7 @@ unpool_dense_kernel(const float* __restrict__ dp, const uint8_t* __restrict__ am
       }
       reinterpret_cast<float4*>(db_part + (size_t)blockIdx.x * C2)[threadIdx.x] = t;
     }
+    if (db_gpart) group_reduce_rows(db_part, C2, C2, db_gpart, counters);
   }
 }
 
@@ -324,9 +325,19 @@ extern "C" int b200_unpool_dense(const float* dp, const uint8_t* amax, float* dy
   const size_t n4 = (size_t)batch * HP * WP * (C2 / 4);
   const int grid = (int)min((size_t)(2 * sm_count()), (n4 + 255) / 256);
   cudaStream_t s = (cudaStream_t)stream;
-  B200_CHECK(b200_launch(unpool_dense_kernel, dim3(grid), dim3(256), 0, s, dp, amax, dy, batch, db_part));
+  B200_CHECK(b200_launch(unpool_dense_kernel, dim3(grid), dim3(256), 0, s, dp, amax, dy, batch, db_part, (float*)nullptr,
+                         (unsigned int*)nullptr));
   b200_count_launch();
   if (db) b200_launch_reduce_partials(db, db_part, C2, grid, C2, s);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+int b200_unpool_dense_grouped(const float* dp, const uint8_t* amax, float* dy, float* db_part, float* db_gpart,
+                              unsigned int* counters, int batch, cudaStream_t s) {
+  B200_REQUIRE(db_part && db_gpart && counters, "unpool_dense_grouped: bad arguments");
+  B200_CHECK(b200_launch(unpool_dense_kernel, dim3(b200_unpool_nparts(batch)), dim3(256), 0, s, dp, amax, dy, batch, db_part,
+                         db_gpart, counters));
+  b200_count_launch();
   B200_LAUNCH_CHECK();
   return B200_OK;
 }

@@ -59,29 +59,74 @@ __global__ void zero_eval_kernel(double* acc) { acc[0] = 0.0; acc[1] = 0.0; }
     if (_r != B200_OK) return _r; \
   } while (0)
 
+// Timeline tracing (B200_TRACE=<step>): in eager mode a timing event is recorded on the launching stream
+// after every kernel of that step; the step is held back by a delay kernel until everything is enqueued,
+// so the printed times show which kernels overlap on the GPU rather than host launch latency.
+struct TraceMark { const char* what; cudaEvent_t ev; int lane; };
+std::vector<TraceMark> g_trace;
+Engine* g_trace_engine = nullptr;
+cudaStream_t g_trace_main = nullptr;
+
+__global__ void trace_delay_kernel(unsigned long long ns) {
+  unsigned long long t0, t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+  do { asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); } while (t - t0 < ns);
+}
+
+void trace_mark(Engine* E, const char* what, cudaStream_t st) {
+  if (g_trace_engine != E) return;
+  cudaEvent_t ev;
+  if (cudaEventCreate(&ev) != cudaSuccess) return;
+  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+  cudaStreamIsCapturing(st, &cap);
+  if (cap == cudaStreamCaptureStatusActive) cudaEventRecordWithFlags(ev, st, cudaEventRecordExternal);  // a graph node
+  else cudaEventRecord(ev, st);
+  g_trace.push_back({what, ev, st == g_trace_main ? 0 : (st == E->br[0] ? 1 : (st == E->br[1] ? 2 : 3))});
+}
+
+ void trace_print(long step, int batch, const char* how) {
+  fprintf(stderr, "[b200 trace] step %ld, batch %d (%s): end-of-kernel times in us (lane 0 = main stream, 1/2 = branches)\n",
+          step, batch, how);
+  for (size_t i = 1; i < g_trace.size(); ++i) {
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, g_trace[0].ev, g_trace[i].ev);
+    char name[48];
+    snprintf(name, sizeof(name), "%.47s", g_trace[i].what);
+    if (char* q = strchr(name, '(')) *q = 0;
+    fprintf(stderr, "[b200 trace]   lane %d  %8.2f  %s\n", g_trace[i].lane, ms * 1000.f, name);
+  }
+}
+
+#define TRYM(x, st)               \
+  do {                            \
+    int _r = (x);                 \
+    if (_r != B200_OK) return _r; \
+    trace_mark(E, #x, st);        \
+  } while (0)
+
 // Forward through the head.  `ctrl` decides train/eval behaviour of the dropout epilogues.
 int enqueue_forward(Engine* E, const uint8_t* images, const uint8_t* labels, const int32_t* idx, const B200Ctrl* ctrl,
                     int batch, bool train, cudaStream_t s) {
   const B200EngineConfig& c = E->cfg;
   float* P = E->P;
-  TRY(b200_conv1_fwd(images, idx, ctrl, P + c.offsets[0], P + c.offsets[1], E->a1, batch, s));
+  TRYM(b200_conv1_fwd(images, idx, ctrl, P + c.offsets[0], P + c.offsets[1], E->a1, batch, s), s);
   if ((E->use_tc & B200_TC_CONV2_FWD) && (E->use_tc & B200_TC_CONV2_V3))
-    TRY(b200_conv2_fwd_tc3(E->a1, P + c.offsets[2], P + c.offsets[3], ctrl, E->pooled, E->amax, batch, s));
+    TRYM(b200_conv2_fwd_tc3(E->a1, P + c.offsets[2], P + c.offsets[3], ctrl, E->pooled, E->amax, batch, s), s);
   else if ((E->use_tc & B200_TC_CONV2_FWD) && (E->use_tc & B200_TC_CONV2_V2))
-    TRY(b200_conv2_fwd_tc2(E->a1, P + c.offsets[2], P + c.offsets[3], ctrl, E->pooled, E->amax, batch, s));
+    TRYM(b200_conv2_fwd_tc2(E->a1, P + c.offsets[2], P + c.offsets[3], ctrl, E->pooled, E->amax, batch, s), s);
   else if (E->use_tc & B200_TC_CONV2_FWD)
-    TRY(b200_conv2_fwd_tc(E->a1, P + c.offsets[2], P + c.offsets[3], ctrl, E->pooled, E->amax, batch, s));
+    TRYM(b200_conv2_fwd_tc(E->a1, P + c.offsets[2], P + c.offsets[3], ctrl, E->pooled, E->amax, batch, s), s);
   else
-    TRY(b200_conv2_fwd_simt(E->a1, P + c.offsets[2], P + c.offsets[3], ctrl, E->pooled, E->amax, batch, s));
+    TRYM(b200_conv2_fwd_simt(E->a1, P + c.offsets[2], P + c.offsets[3], ctrl, E->pooled, E->amax, batch, s), s);
   const int splits = fc1_splits(batch);
   if (E->use_tc & B200_TC_FC1_FWD)
-    TRY(b200_tc_gemm(E->pooled, P + c.offsets[4], E->fc1_part, batch, FC1_OUT, FC1_IN, 0, 0, splits, 0, nullptr, 0.f, s));
+    TRYM(b200_tc_gemm(E->pooled, P + c.offsets[4], E->fc1_part, batch, FC1_OUT, FC1_IN, 0, 0, splits, 0, nullptr, 0.f, s), s);
   else
-    TRY(b200_sgemm(E->pooled, FC1_IN, 1, P + c.offsets[4], 1, FC1_IN, E->fc1_part, batch, FC1_OUT, FC1_IN, splits, 0,
-                   nullptr, 0.f, s));
-  TRY(b200_head_fused(E->fc1_part, splits, batch, P + c.offsets[5], P + c.offsets[6], P + c.offsets[7], labels, idx,
+    TRYM(b200_sgemm(E->pooled, FC1_IN, 1, P + c.offsets[4], 1, FC1_IN, E->fc1_part, batch, FC1_OUT, FC1_IN, splits, 0,
+                   nullptr, 0.f, s), s);
+  TRYM(b200_head_fused(E->fc1_part, splits, batch, P + c.offsets[5], P + c.offsets[6], P + c.offsets[7], labels, idx,
                       ctrl, E->h, train ? E->dlogits : nullptr, train ? E->dh : nullptr, E->loss_i,
-                      train ? nullptr : E->correct_i, train ? nullptr : E->logp, s));
+                      train ? nullptr : E->correct_i, train ? nullptr : E->logp, s), s);
   return B200_OK;
 }
 
@@ -98,23 +143,50 @@ int enqueue_train(Engine* E, const uint8_t* images, const uint8_t* labels, const
   const bool fuse_unpool = want_fused_unpool && (E->use_tc & B200_TC_FC1_BWD) && (E->use_tc & B200_TC_CONV2_BWD) &&
                            (E->hooks.bucket_ready != nullptr || !E->defer_update);
   TRY(enqueue_forward(E, images, labels, idx, E->ctrl, batch, true, s));
-  TRY(b200_head_wgrad(E->h, E->dlogits, E->dh, E->loss_i, batch, G + c.offsets[6], G + c.offsets[7], G + c.offsets[5],
-                      E->loss_scalar, E->ctrl, E->loss_ring, B200_LOSS_RING, E->loss_ring_host_dev, s));
-  // fc1: dW1[128][9216] = dh^T . pooled ; dp = (dh . W1) * (pooled > 0 ? 1/(1-p1) : 0)
+  // Fork: the head's weight gradients and the fc1 wgrad GEMM only feed the optimizer, so they leave the
+  // critical path (fc1 dgrad -> un-pool -> conv2 dgrad -> conv1 wgrad) and run next to it.
+  const bool par = E->branches && E->br[0] != nullptr;
+  cudaStream_t sw = par ? E->br[0] : s;
+  if (par) {
+    B200_CHECK(cudaEventRecord(E->ev_head, s));
+    B200_CHECK(cudaStreamWaitEvent(sw, E->ev_head, 0));
+  }
+  // fc1: dp = (dh . W1) * (pooled > 0 ? 1/(1-p1) : 0)   -- critical path, enqueued first
   if (E->use_tc & B200_TC_FC1_BWD) {
-    TRY(b200_tc_gemm(E->dh, E->pooled, G + c.offsets[4], FC1_OUT, FC1_IN, batch, 1, 1, 1, 0, nullptr, 0.f, s));
     if (fuse_unpool)  // dgrad writes the dense dY (and conv2 bias-gradient partials) itself
-      TRY(b200_fc1_dgrad_unpool_tc(E->dh, P + c.offsets[4], E->pooled, E->amax, E->dy, E->db_part, batch, drop1_scale, s));
+      TRYM(b200_fc1_dgrad_unpool_tc(E->dh, P + c.offsets[4], E->pooled, E->amax, E->dy, E->db_part, batch, drop1_scale, s), s);
     else
-      TRY(b200_tc_gemm(E->dh, P + c.offsets[4], E->dp, batch, FC1_IN, FC1_OUT, 0, 1, 1, 1, E->pooled, drop1_scale, s));
+      TRYM(b200_tc_gemm(E->dh, P + c.offsets[4], E->dp, batch, FC1_IN, FC1_OUT, 0, 1, 1, 1, E->pooled, drop1_scale, s), s);
   } else {
-    TRY(b200_sgemm(E->dh, 1, FC1_OUT, E->pooled, FC1_IN, 1, G + c.offsets[4], FC1_OUT, FC1_IN, batch, 1, 0, nullptr,
-                   0.f, s));
-    TRY(b200_sgemm(E->dh, FC1_OUT, 1, P + c.offsets[4], FC1_IN, 1, E->dp, batch, FC1_IN, FC1_OUT, 1, 1, E->pooled,
-                   drop1_scale, s));
+    TRYM(b200_sgemm(E->dh, FC1_OUT, 1, P + c.offsets[4], FC1_IN, 1, E->dp, batch, FC1_IN, FC1_OUT, 1, 1, E->pooled,
+                   drop1_scale, s), s);
+  }
+  // dW2, db2, db1, mean loss; fc1: dW1[128][9216] = dh^T . pooled
+  TRYM(b200_head_wgrad(E->h, E->dlogits, E->dh, E->loss_i, batch, G + c.offsets[6], G + c.offsets[7], G + c.offsets[5],
+                      E->loss_scalar, E->ctrl, E->loss_ring, B200_LOSS_RING, E->loss_ring_host_dev, sw), sw);
+  if (E->use_tc & B200_TC_FC1_BWD)
+    TRYM(b200_tc_gemm(E->dh, E->pooled, G + c.offsets[4], FC1_OUT, FC1_IN, batch, 1, 1, 1, 0, nullptr, 0.f, sw), sw);
+  else
+    TRYM(b200_sgemm(E->dh, 1, FC1_OUT, E->pooled, FC1_IN, 1, G + c.offsets[4], FC1_OUT, FC1_IN, batch, 1, 0, nullptr,
+                   0.f, sw), sw);
+  const bool own_update = !E->hooks.bucket_ready && !E->defer_update;
+  bool fc_updated = false;
+  if (par) {
+    B200_CHECK(cudaEventRecord(E->ev_fcw, sw));
+    if (own_update) {
+      // single GPU: the fc bucket (98 % of the parameters) gets its Adadelta update on the branch, under
+      // the conv backward; it may only start once fc1 dgrad has read the old fc1.weight
+      B200_CHECK(cudaEventRecord(E->ev_fcd, s));
+      B200_CHECK(cudaStreamWaitEvent(sw, E->ev_fcd, 0));
+      TRYM(b200_adadelta(P, G, E->V, E->U, c.bucket_begin[1], E->ctrl, 0.9f, 1e-6f, -1, nullptr, sw), sw);
+      B200_CHECK(cudaEventRecord(E->ev_fcu, sw));
+      fc_updated = true;
+    } else {
+      B200_CHECK(cudaStreamWaitEvent(s, E->ev_fcw, 0));  // the bucket hook / the caller needs the whole fc bucket
+    }
   }
   // bucket 0 (fc1.*, fc2.*) is complete here
-  if (E->hooks.bucket_ready) TRY(E->hooks.bucket_ready(E, 0, s));
+  if (E->hooks.bucket_ready) TRYM(E->hooks.bucket_ready(E, 0, s), s);
   // With data-parallel hooks the conv-bucket gradients are left as per-CTA partials: the step's last
   // kernel reduces them, all-reduces, and applies Adadelta in one go (fin).
   const bool fuse = E->hooks.bucket_ready != nullptr || !E->defer_update;
@@ -122,41 +194,65 @@ int enqueue_train(Engine* E, const uint8_t* images, const uint8_t* labels, const
   float* dw2 = fuse ? nullptr : G + c.offsets[2];
   float* db2 = fuse ? nullptr : G + c.offsets[3];
   int np2 = 0;
+  bool c2w_pending = false;
   if (E->use_tc & B200_TC_CONV2_BWD) {
-    if (!fuse_unpool) TRY(b200_unpool_dense(E->dp, E->amax, E->dy, E->db_part, db2, batch, s));
-    if (E->use_tc & B200_TC_CONV2_V2) {
-      TRY(b200_conv2_wgrad_tc2(E->dy, E->a1, E->c2_part, dw2, batch, s));
-      if (E->use_tc & B200_TC_CONV2_V3) TRY(b200_conv2_dgrad_tc3(E->dy, P + c.offsets[2], E->a1, E->da1, batch, s));
-      else TRY(b200_conv2_dgrad_tc2(E->dy, P + c.offsets[2], E->a1, E->da1, batch, s));
-      np2 = min(3 * batch, E->nsm);
-    } else {
-      TRY(b200_conv2_wgrad_tc(E->dy, E->a1, E->c2_part, dw2, batch, s));
-      TRY(b200_conv2_dgrad_tc(E->dy, P + c.offsets[2], E->a1, E->da1, batch, s));
-      np2 = min(9 * batch, E->nsm);
+    if (!fuse_unpool) {
+      if (fuse) TRYM(b200_unpool_dense_grouped(E->dp, E->amax, E->dy, E->db_part, E->db_gpart, E->db_cnt, batch, s), s);
+      else TRYM(b200_unpool_dense(E->dp, E->amax, E->dy, E->db_part, db2, batch, s), s);
+    }
+    // Fork: conv2 wgrad and conv2 dgrad both read dY; wgrad runs beside dgrad / conv1 wgrad
+    cudaStream_t sc = par ? E->br[1] : s;
+    if (par) {
+      B200_CHECK(cudaEventRecord(E->ev_dy, s));
+      B200_CHECK(cudaStreamWaitEvent(sc, E->ev_dy, 0));
+    }
+    // with branches the critical-path kernel (dgrad) is enqueued first so that it gets the SMs first
+    for (int pass = 0; pass < 2; ++pass) {
+      const bool do_wgrad = (pass == 0) != par;
+      if (E->use_tc & B200_TC_CONV2_V2) {
+        if (do_wgrad) TRYM(b200_conv2_wgrad_tc2(E->dy, E->a1, E->c2_part, dw2, batch, sc), sc);
+        else if (E->use_tc & B200_TC_CONV2_V3) TRYM(b200_conv2_dgrad_tc3(E->dy, P + c.offsets[2], E->a1, E->da1, batch, s), s);
+        else TRYM(b200_conv2_dgrad_tc2(E->dy, P + c.offsets[2], E->a1, E->da1, batch, s), s);
+      } else {
+        if (do_wgrad) TRYM(b200_conv2_wgrad_tc(E->dy, E->a1, E->c2_part, dw2, batch, sc), sc);
+        else TRYM(b200_conv2_dgrad_tc(E->dy, P + c.offsets[2], E->a1, E->da1, batch, s), s);
+      }
+    }
+    np2 = min(((E->use_tc & B200_TC_CONV2_V2) ? 3 : 9) * batch, E->nsm);
+    if (par) {
+      B200_CHECK(cudaEventRecord(E->ev_c2w, sc));
+      c2w_pending = true;
     }
     if (fuse_unpool)  // partial rows = (128-sample tile, pooled pixel): [ceil(B/128)*144][64]
       E->fin.seg[1] = {E->db_part, ceil_div(batch, 128) * HP * WP, C2, C2, (int)(c.offsets[3] - b1)};
     else
-      E->fin.seg[1] = {E->db_part, b200_unpool_nparts(batch), C2, C2, (int)(c.offsets[3] - b1)};
+      E->fin.seg[1] = {E->db_gpart, b200_group_count(b200_unpool_nparts(batch)), C2, C2, (int)(c.offsets[3] - b1)};
   } else {
-    TRY(b200_conv2_wgrad_simt(E->dp, E->amax, E->a1, E->c2_part, dw2, db2, batch, s));
-    TRY(b200_conv2_dgrad_simt(E->dp, E->amax, P + c.offsets[2], E->a1, E->da1, batch, s));
+    TRYM(b200_conv2_wgrad_simt(E->dp, E->amax, E->a1, E->c2_part, dw2, db2, batch, s), s);
+    TRYM(b200_conv2_dgrad_simt(E->dp, E->amax, P + c.offsets[2], E->a1, E->da1, batch, s), s);
     np2 = min(9 * batch, E->nsm);
     E->fin.seg[1] = {E->c2_part + 9 * C2 * C1, np2, 9 * C2 * C1 + C2, C2, (int)(c.offsets[3] - b1)};
   }
   E->fin.seg[0] = {E->c2_part, np2, 9 * C2 * C1 + C2, 9 * C2 * C1, (int)(c.offsets[2] - b1)};
-  TRY(b200_conv1_wgrad(images, idx, E->ctrl, E->da1, E->c1_part, fuse ? nullptr : G + c.offsets[0],
-                       fuse ? nullptr : G + c.offsets[1], batch, s));
-  E->fin.seg[2] = {E->c1_part, 2 * batch, 320, 288, (int)(c.offsets[0] - b1)};
-  E->fin.seg[3] = {E->c1_part + 288, 2 * batch, 320, 32, (int)(c.offsets[1] - b1)};
+  if (fuse) {
+    TRYM(b200_conv1_wgrad_grouped(images, idx, E->ctrl, E->da1, E->c1_part, E->c1_gpart, E->c1_cnt, batch, s), s);
+    const int ng = b200_group_count(2 * batch);
+    E->fin.seg[2] = {E->c1_gpart, ng, 320, 288, (int)(c.offsets[0] - b1)};
+    E->fin.seg[3] = {E->c1_gpart + 288, ng, 320, 32, (int)(c.offsets[1] - b1)};
+  } else {
+    TRYM(b200_conv1_wgrad(images, idx, E->ctrl, E->da1, E->c1_part, G + c.offsets[0], G + c.offsets[1], batch, s), s);
+  }
   E->fin_valid = fuse;
+  // Join: everything the step's last kernel(s) read must be complete
+  if (c2w_pending) B200_CHECK(cudaStreamWaitEvent(s, E->ev_c2w, 0));
+  if (fc_updated) B200_CHECK(cudaStreamWaitEvent(s, E->ev_fcu, 0));
   if (E->hooks.bucket_ready) {
-    TRY(E->hooks.bucket_ready(E, 1, s));
-    TRY(E->hooks.step_end(E, advance, s));
+    TRYM(E->hooks.bucket_ready(E, 1, s), s);
+    TRYM(E->hooks.step_end(E, advance, s), s);
   } else if (!E->defer_update) {
     // bucket 0 occupies floats [0, bucket_begin[1]) of the flat layout, bucket 1 the rest
-    TRY(b200_adadelta_finalize(P, G, E->V, E->U, b1, (int)((c.bucket_end[1] - b1) / 256), E->fin, E->ctrl, 0.9f,
-                               1e-6f, advance, E->done_counter, s));
+    TRYM(b200_adadelta_finalize(P, G, E->V, E->U, b1, (int)((c.bucket_end[1] - b1) / 256), E->fin, E->ctrl, 0.9f,
+                               1e-6f, advance, E->done_counter, fc_updated, s), s);
   }
   return B200_OK;
 }
@@ -173,7 +269,24 @@ std::map<std::pair<Engine*, GraphKey>, GraphVal> g_graphs;
 
 int run_step(Engine* E, const uint8_t* images, const uint8_t* labels, const int32_t* idx, int batch, int advance,
              int mode, int use_graph, cudaStream_t s) {
-  if (!use_graph) return enqueue_train(E, images, labels, idx, batch, advance, s);
+  if (!use_graph) {
+    static const long trace_step = getenv("B200_TRACE") ? atol(getenv("B200_TRACE")) : -1;
+    if (trace_step < 0 || (long)E->steps != trace_step) return enqueue_train(E, images, labels, idx, batch, advance, s);
+    B200_CHECK(cudaDeviceSynchronize());
+    g_trace.clear();
+    g_trace_engine = E;
+    g_trace_main = s;
+    trace_delay_kernel<<<1, 1, 0, s>>>(300000ull);
+    trace_mark(E, "start", s);
+    int r = enqueue_train(E, images, labels, idx, batch, advance, s);
+    g_trace_engine = nullptr;
+    B200_CHECK(cudaDeviceSynchronize());
+    trace_print(trace_step, batch, "eager");
+    for (auto& m : g_trace) cudaEventDestroy(m.ev);
+    g_trace.clear();
+    return r;
+  }
+  static const long trace_step_g = getenv("B200_TRACE") ? atol(getenv("B200_TRACE")) : -1;
   mode += (E->dropout ? 0 : 8) + (E->defer_update ? 16 : 0);
   auto key = std::make_pair(E, GraphKey{batch, mode});
   auto it = g_graphs.find(key);
@@ -185,7 +298,14 @@ int run_step(Engine* E, const uint8_t* images, const uint8_t* labels, const int3
     cudaGraph_t graph = nullptr;
     const long long before = b200_launch_count();
     B200_CHECK(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
+    const bool traced = trace_step_g >= 0 && g_trace.empty();  // timing events become nodes of the first captured graph
+    if (traced) {
+      g_trace_engine = E;
+      g_trace_main = s;
+      trace_mark(E, "start", s);
+    }
     int r = enqueue_train(E, images, labels, idx, batch, advance, s);
+    g_trace_engine = nullptr;
     cudaError_t ce = cudaStreamEndCapture(s, &graph);
     if (r != B200_OK) {
       if (graph) cudaGraphDestroy(graph);
@@ -200,6 +320,10 @@ int run_step(Engine* E, const uint8_t* images, const uint8_t* labels, const int3
   }
   B200_CHECK(cudaGraphLaunch(it->second.exec, s));
   b200_count_launch(it->second.kernels);
+  if (trace_step_g >= 0 && (long)E->steps == trace_step_g && !g_trace.empty()) {
+    B200_CHECK(cudaStreamSynchronize(s));
+    trace_print(trace_step_g, batch, "graph replay");
+  }
   return B200_OK;
 }
 
@@ -249,6 +373,10 @@ extern "C" int b200_engine_create(const B200EngineConfig* cfg, void** out) {
   for (int b = 1; b <= cfg->max_batch; ++b) part_cap = max(part_cap, (size_t)fc1_splits(b) * b * FC1_OUT);
   A(E->fc1_part, part_cap);
   A(E->c1_part, 2 * B * 320);
+  A(E->c1_gpart, (size_t)b200_group_count(2 * cfg->max_batch) * 320);
+  A(E->c1_cnt, (size_t)b200_group_count(2 * cfg->max_batch));
+  A(E->db_gpart, (size_t)b200_group_count(b200_unpool_parts()) * C2);
+  A(E->db_cnt, (size_t)b200_group_count(b200_unpool_parts()));
   A(E->c2_part, (size_t)E->nsm * (9 * C2 * C1 + C2));
   if (cfg->use_tc & B200_TC_CONV2_BWD) A(E->dy, B * H2 * W2 * C2);
   A(E->db_part, max((size_t)b200_unpool_parts() * C2, (size_t)ceil_div(cfg->max_batch, 128) * FC1_IN));
@@ -264,6 +392,10 @@ extern "C" int b200_engine_create(const B200EngineConfig* cfg, void** out) {
   B200_CHECK(cudaHostAlloc((void**)&E->loss_ring_host, B200_LOSS_RING * sizeof(float), cudaHostAllocMapped));
   memset(E->loss_ring_host, 0, B200_LOSS_RING * sizeof(float));
   B200_CHECK(cudaHostGetDevicePointer((void**)&E->loss_ring_host_dev, E->loss_ring_host, 0));
+  E->branches = !(getenv("B200_NO_BRANCH") && atoi(getenv("B200_NO_BRANCH")) == 1);
+  for (int i = 0; i < 2; ++i) B200_CHECK(cudaStreamCreateWithFlags(&E->br[i], cudaStreamNonBlocking));
+  for (cudaEvent_t* e : {&E->ev_head, &E->ev_fcw, &E->ev_fcd, &E->ev_fcu, &E->ev_dy, &E->ev_c2w})
+    B200_CHECK(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
   const float inv_w = 1.0f / (float)(cfg->world > 0 ? cfg->world : 1);
   TRY(b200_ctrl_set(E->ctrl, 0, cfg->seed, 0, 3, 1.0f, inv_w, nullptr));
   TRY(b200_ctrl_set(E->ctrl_eval, 0, cfg->seed, 0, 0, 0.0f, inv_w, nullptr));
@@ -281,6 +413,8 @@ extern "C" int b200_engine_destroy(void* engine) {
     else ++it;
   }
   if (E->hooks.destroy) E->hooks.destroy(E);
+  for (int i = 0; i < 2; ++i) if (E->br[i]) cudaStreamDestroy(E->br[i]);
+  for (cudaEvent_t e : {E->ev_head, E->ev_fcw, E->ev_fcd, E->ev_fcu, E->ev_dy, E->ev_c2w}) if (e) cudaEventDestroy(e);
   if (E->copy_stream) {
     cudaStreamDestroy(E->copy_stream);
     for (int i = 0; i < 2; ++i) { cudaEventDestroy(E->ev_copied[i]); cudaEventDestroy(E->ev_consumed[i]); }

@@ -11,13 +11,15 @@ enum { B200_TC_CONV2_FWD = 1, B200_TC_FC1_FWD = 2, B200_TC_FC1_BWD = 4, B200_TC_
 // Where the conv bucket's gradients still sit as per-CTA partial sums at the end of backward.  The
 // last kernel of the step (allreduce.cu: finalize_bucket_kernel) reduces them itself, so no separate
 // reduction kernels sit on the critical path.  dst_off: float offset inside the bucket (x256).
+constexpr int FIN_SLICES = 16;  // the finalize kernels run 64 float4 columns x FIN_SLICES row slices per CTA
 struct FinalizeSegs {
   struct Seg { const float* src; int nparts, stride, n, dst_off; } seg[4];
 };
 
 // adadelta.cu: single-GPU end of step = partial reduction of the conv bucket + Adadelta on everything
 int b200_adadelta_finalize(float* p, float* g, float* v, float* u, long b1_off, int nchunks, const FinalizeSegs& segs,
-                           void* ctrl, float rho, float eps, int advance, unsigned int* done_counter, cudaStream_t s);
+                           void* ctrl, float rho, float eps, int advance, unsigned int* done_counter, bool bucket0_done,
+                           cudaStream_t s);
 
 struct Engine;
 struct EngineHooks {
@@ -43,6 +45,8 @@ struct Engine {
   float *a1 = nullptr, *da1 = nullptr, *pooled = nullptr, *dp = nullptr, *h = nullptr, *dh = nullptr,
         *dlogits = nullptr, *loss_i = nullptr, *logp = nullptr, *fc1_part = nullptr, *c1_part = nullptr,
         *c2_part = nullptr, *dy = nullptr, *db_part = nullptr, *loss_ring = nullptr, *loss_scalar = nullptr;
+  float *c1_gpart = nullptr, *db_gpart = nullptr;      // group-combined partial rows (common.cuh: group_reduce_rows)
+  unsigned int *c1_cnt = nullptr, *db_cnt = nullptr;   // their arrival counters
   uint8_t* amax = nullptr;
   int* correct_i = nullptr;
   B200Ctrl *ctrl = nullptr, *ctrl_eval = nullptr;
@@ -57,6 +61,12 @@ struct Engine {
   cudaStream_t copy_stream = nullptr;  // H2D staging for train_step_host (double buffered)
   cudaEvent_t ev_copied[2] = {nullptr, nullptr}, ev_consumed[2] = {nullptr, nullptr};
   bool consumed_valid[2] = {false, false};
+  // Independent kernels of the backward pass run on two branch streams (forked and joined with
+  // events, so the whole step is still one capturable graph): br[0] = head wgrad, fc1 wgrad and the
+  // fc bucket's Adadelta, br[1] = conv2 wgrad.
+  cudaStream_t br[2] = {nullptr, nullptr};
+  cudaEvent_t ev_head = nullptr, ev_fcw = nullptr, ev_fcd = nullptr, ev_fcu = nullptr, ev_dy = nullptr, ev_c2w = nullptr;
+  bool branches = true;
   EngineHooks hooks;
   FinalizeSegs fin{};       // filled by enqueue_train when fin_valid
   bool fin_valid = false;

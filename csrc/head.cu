@@ -41,9 +41,21 @@ head_fused_kernel(const float* __restrict__ part, int splits, int batch,      //
 
   // ---- fc1 epilogue: reduce split-K partials in a fixed order
   float4 z = *reinterpret_cast<const float4*>(b1 + lane * 4);
-  for (int s = 0; s < splits; ++s) {
-    const float4 p = *reinterpret_cast<const float4*>(part + ((size_t)s * batch + b) * FC1_OUT + lane * 4);
-    z.x += p.x; z.y += p.y; z.z += p.z; z.w += p.w;
+  {
+    const float* src = part + (size_t)b * FC1_OUT + lane * 4;
+    const size_t pitch = (size_t)batch * FC1_OUT;
+    int s = 0;
+    for (; s + 6 <= splits; s += 6) {  // six loads in flight, summed in split order
+      float4 p[6];
+#pragma unroll
+      for (int j = 0; j < 6; ++j) p[j] = *reinterpret_cast<const float4*>(src + (size_t)(s + j) * pitch);
+#pragma unroll
+      for (int j = 0; j < 6; ++j) { z.x += p[j].x; z.y += p[j].y; z.z += p[j].z; z.w += p[j].w; }
+    }
+    for (; s < splits; ++s) {
+      const float4 p = *reinterpret_cast<const float4*>(src + (size_t)s * pitch);
+      z.x += p.x; z.y += p.y; z.z += p.z; z.w += p.w;
+    }
   }
   float hv[4] = {fmaxf(z.x, 0.f), fmaxf(z.y, 0.f), fmaxf(z.z, 0.f), fmaxf(z.w, 0.f)};
   if (train & 2) {
@@ -184,7 +196,9 @@ extern "C" int b200_head_fused(const float* part, int splits, int batch, const f
                                float* h, float* dlogits, float* dh, float* loss_i, int* correct_i, float* logp,
                                void* stream) {
   B200_REQUIRE(batch > 0 && splits > 0, "head_fused: bad batch/splits");
-  B200_CHECK(b200_launch(head_fused_kernel, dim3(ceil_div(batch, 8)), dim3(256), 0, (cudaStream_t)stream, part, splits,
+  // small batches: two samples per CTA so that the split-K reduction is spread over ~100 SMs
+  const int warps = batch <= 1024 ? 2 : 8;
+  B200_CHECK(b200_launch(head_fused_kernel, dim3(ceil_div(batch, warps)), dim3(32 * warps), 0, (cudaStream_t)stream, part, splits,
                          batch, b1, w2, b2, labels, idx, (const B200Ctrl*)ctrl, h, dlogits, dh, loss_i, correct_i, logp));
   b200_count_launch();
   B200_LAUNCH_CHECK();

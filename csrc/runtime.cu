@@ -3,6 +3,8 @@
 #include <cstdarg>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
+#include <unordered_set>
 
 #include "common.cuh"
 
@@ -23,6 +25,15 @@ bool b200_pdl_enabled() {
   // the hidden launch latency saves, and graph replay was no longer bit-identical to eager launches.
   static const bool on = getenv("B200_PDL") && atoi(getenv("B200_PDL")) == 1;
   return on;
+}
+
+void b200_prefer_max_shared(const void* kernel) {
+  static std::mutex mu;
+  static std::unordered_set<const void*> seen;
+  std::lock_guard<std::mutex> lock(mu);
+  if (!seen.insert(kernel).second) return;
+  static const bool off = getenv("B200_NO_CARVEOUT") != nullptr;  // diagnostics
+  if (!off) cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
 }
 
 int b200_sm_count() {

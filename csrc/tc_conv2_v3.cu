@@ -36,7 +36,7 @@ constexpr int DG_SMEM = 9 * TAP_BYTES + 2 * PATCH_BYTES + 1024;
 // one half empty).  The patch holds dY rows y0-2 .. y0+15, columns 0..31 (24 real, zero beyond).
 __global__ void __launch_bounds__(320, 1)
 conv2_dgrad_tc3_kernel(const __grid_constant__ CUtensorMap mapDY, const __grid_constant__ CUtensorMap mapW,
-                       const float* __restrict__ a1, float* __restrict__ da1, int nitems) {
+                       const float* __restrict__ a1, float* __restrict__ da1, int nitems, int flags) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   uint8_t* wsm = smem;                     // [kh][kw][64 o][32 i], 32B-atom swizzle: N-major B operand
@@ -66,6 +66,11 @@ conv2_dgrad_tc3_kernel(const __grid_constant__ CUtensorMap mapDY, const __grid_c
   const uint32_t tmem_base = tmem_base_smem;
   pdl_wait();  // on-chip set-up above overlaps the previous kernel's tail
   const int my_items = (nitems - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+  // Items alternate between 4-tile (upper half) and 3-tile (lower half) work.  With an even grid a CTA
+  // would see the same half in every round (12 tiles against 9); swapping neighbours in odd rounds gives
+  // every CTA both kinds (11 against 10).  nitems and the grid are even, so pairs stay inside a round.
+  const bool flip = (gridDim.x & 1) == 0 && (flags & 1);
+  auto item_of = [&](int it) { return (int)(blockIdx.x + it * gridDim.x) ^ ((flip && (it & 1)) ? 1 : 0); };
 
   if (warp == 0) {
     const bool leader = elect_one();
@@ -73,7 +78,7 @@ conv2_dgrad_tc3_kernel(const __grid_constant__ CUtensorMap mapDY, const __grid_c
     for (int t = 0; t < 9; ++t)
       if (leader) tma_load_2d(wsm + t * TAP_BYTES, &mapW, &w_bar, 0, t * 64);
     for (int it = 0; it < my_items; ++it) {
-      const int item = blockIdx.x + it * gridDim.x, n = item >> 1, y0 = (item & 1) * 16;
+      const int item = item_of(it), n = item >> 1, y0 = (item & 1) * 16;
       for (int kc = 0; kc < 2; ++kc) {
         mbar_wait(&pempty[kc], (it & 1) ^ 1);
         if (leader) mbar_expect_tx(&pfull[kc], PATCH_BYTES);
@@ -87,7 +92,7 @@ conv2_dgrad_tc3_kernel(const __grid_constant__ CUtensorMap mapDY, const __grid_c
     mbar_wait(&w_bar, 0);
     int tc_ = 0;  // running tile counter -> TMEM slot
     for (int it = 0; it < my_items; ++it) {
-      const int ntile = ((blockIdx.x + it * gridDim.x) & 1) ? 3 : 4;
+      const int ntile = (item_of(it) & 1) ? 3 : 4;
       // chunk-major order: all tiles of the item consume channel chunk 0, then chunk 1
       for (int kc = 0; kc < 2; ++kc) {
         mbar_wait(&pfull[kc], it & 1);
@@ -121,10 +126,19 @@ conv2_dgrad_tc3_kernel(const __grid_constant__ CUtensorMap mapDY, const __grid_c
     const int q = wq, hc = (warp - 2) >> 2;
     int tc_ = 0;
     for (int it = 0; it < my_items; ++it) {
-      const int item = blockIdx.x + it * gridDim.x, n = item >> 1, half = item & 1, y0 = half * 16;
+      const int item = item_of(it), n = item >> 1, half = item & 1, y0 = half * 16;
       const int ntile = half ? 3 : 4;
       for (int t = 0; t < ntile; ++t) {
         const int slot = (tc_ + t) & 3;
+        // the ReLU mask (conv1's output) does not depend on the MMAs: fetch it before waiting for them
+        const int y = y0 + 4 * t + q, x = lane;
+        const bool valid = y < H1 && x < W1;
+        const size_t e = (((size_t)n * H1 + (valid ? y : 0)) * W1 + (valid ? x : 0)) * C1 + hc * 16;
+        float4 am[4];
+        if (flags & 2) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) am[j] = *reinterpret_cast<const float4*>(a1 + e + 4 * j);
+        }
         mbar_wait(&tfull[slot], ((tc_ + t) >> 2) & 1);
         tc_fence_after();
         float v0[16], v1[16], v2[16];
@@ -142,12 +156,14 @@ conv2_dgrad_tc3_kernel(const __grid_constant__ CUtensorMap mapDY, const __grid_c
           const float s2 = __shfl_up_sync(0xffffffffu, v2[j], 2);
           v0[j] += (lane >= 1 ? s1 : 0.f) + (lane >= 2 ? s2 : 0.f);
         }
-        const int y = y0 + 4 * t + q, x = lane;
-        if (y < H1 && x < W1) {
-          const size_t e = (((size_t)n * H1 + y) * W1 + x) * C1 + hc * 16;
+        if (!(flags & 2)) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) am[j] = *reinterpret_cast<const float4*>(a1 + e + 4 * j);
+        }
+        if (valid) {
 #pragma unroll
           for (int j = 0; j < 16; j += 4) {
-            const float4 a = *reinterpret_cast<const float4*>(a1 + e + j);
+            const float4 a = am[j >> 2];
             *reinterpret_cast<float4*>(da1 + e + j) =
                 make_float4(a.x > 0.f ? v0[j] : 0.f, a.y > 0.f ? v0[j + 1] : 0.f, a.z > 0.f ? v0[j + 2] : 0.f,
                             a.w > 0.f ? v0[j + 3] : 0.f);
@@ -177,17 +193,19 @@ constexpr int F_ROW_BYTES = F_PITCH * 128;             // 2 KiB
 constexpr int F_PATCH_BYTES = F_ROWS * F_ROW_BYTES;    // 53,248
 constexpr int F3_SMEM = 9 * TAP_BYTES + 2 * F_PATCH_BYTES + 1024;
 
-// 32 channels of one output pixel per lane -> 2x2 max-pool over (lane^1, lane^16) -> 8 channels of one
-// pooled pixel per lane (channel offset c0) -> bias, ReLU, dropout, store.
-__device__ __forceinline__ void pool32_store(const float (&v)[32], int lane, int oc, const float* bias_s, int train,
-                                             unsigned long long seed, unsigned long long step, uint32_t e_pixel,
-                                             bool store, float* __restrict__ pooled, uint8_t* __restrict__ amax) {
+// NCH (32 or 16) channels of one output pixel per lane -> 2x2 max-pool over (lane^1, lane^16) -> NCH/4
+// channels of one pooled pixel per lane (channel offset c0) -> bias, ReLU, dropout, store.
+template <int NCH>
+__device__ __forceinline__ void pool_store(const float (&v)[NCH], int lane, int oc, const float* bias_s, int train,
+                                           unsigned long long seed, unsigned long long step, uint32_t e_pixel,
+                                           bool store, float* __restrict__ pooled, uint8_t* __restrict__ amax) {
+  constexpr int HA = NCH / 2, HB = NCH / 4;
   const bool b0 = lane & 1, b4 = (lane >> 4) & 1;
-  float m1[16];
+  float m1[HA];
   uint32_t dxmask = 0;
 #pragma unroll
-  for (int j = 0; j < 16; ++j) {
-    const float mine = b0 ? v[16 + j] : v[j], send = b0 ? v[j] : v[16 + j];
+  for (int j = 0; j < HA; ++j) {
+    const float mine = b0 ? v[HA + j] : v[j], send = b0 ? v[j] : v[HA + j];
     const float recv = __shfl_xor_sync(0xffffffffu, send, 1);
     const float ev = b0 ? recv : mine, od = b0 ? mine : recv;
     const bool gt = od > ev;  // strict: first maximum wins
@@ -195,13 +213,13 @@ __device__ __forceinline__ void pool32_store(const float (&v)[32], int lane, int
     dxmask |= (uint32_t)gt << j;
   }
   const uint32_t dx_other = __shfl_xor_sync(0xffffffffu, dxmask, 16);
-  float m2[8];
-  uint32_t am[8];
+  float m2[HB];
+  uint32_t am[HB];
 #pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    const float mine = b4 ? m1[8 + j] : m1[j], send = b4 ? m1[j] : m1[8 + j];
+  for (int j = 0; j < HB; ++j) {
+    const float mine = b4 ? m1[HB + j] : m1[j], send = b4 ? m1[j] : m1[HB + j];
     const float recv = __shfl_xor_sync(0xffffffffu, send, 16);
-    const int jj = (b4 ? 8 : 0) + j;
+    const int jj = (b4 ? HB : 0) + j;
     const uint32_t dxm = (dxmask >> jj) & 1u, dxo = (dx_other >> jj) & 1u;
     const float top = b4 ? recv : mine, bot = b4 ? mine : recv;
     const uint32_t dxt = b4 ? dxo : dxm, dxb = b4 ? dxm : dxo;
@@ -210,10 +228,10 @@ __device__ __forceinline__ void pool32_store(const float (&v)[32], int lane, int
     am[j] = gt ? (2u + dxb) : dxt;
   }
   if (!store) return;
-  const int c0 = oc * 32 + (b0 ? 16 : 0) + (b4 ? 8 : 0);
+  const int c0 = oc * NCH + (b0 ? HA : 0) + (b4 ? HB : 0);
   const uint32_t e = e_pixel + c0;
 #pragma unroll
-  for (int g4 = 0; g4 < 2; ++g4) {
+  for (int g4 = 0; g4 < HB / 4; ++g4) {
     float o[4];
 #pragma unroll
     for (int c = 0; c < 4; ++c) o[c] = fmaxf(m2[g4 * 4 + c] + bias_s[c0 + g4 * 4 + c], 0.f);
@@ -227,13 +245,19 @@ __device__ __forceinline__ void pool32_store(const float (&v)[32], int lane, int
     }
     *reinterpret_cast<float4*>(pooled + e + g4 * 4) = make_float4(o[0], o[1], o[2], o[3]);
   }
-  uint2 pk;
-  pk.x = am[0] | (am[1] << 8) | (am[2] << 16) | (am[3] << 24);
-  pk.y = am[4] | (am[5] << 8) | (am[6] << 16) | (am[7] << 24);
-  *reinterpret_cast<uint2*>(amax + e) = pk;
+  if (HB == 8) {
+    uint2 pk;
+    pk.x = am[0] | (am[1] << 8) | (am[2] << 16) | (am[3] << 24);
+    pk.y = am[HB - 4] | (am[HB - 3] << 8) | (am[HB - 2] << 16) | (am[HB - 1] << 24);
+    *reinterpret_cast<uint2*>(amax + e) = pk;
+  } else {
+    *reinterpret_cast<uint32_t*>(amax + e) = am[0] | (am[1] << 8) | (am[2] << 16) | (am[3] << 24);
+  }
 }
 
-__global__ void __launch_bounds__(320, 1)
+// EW = number of epilogue warps: 8 (32 channels per warp) or 16 (16 channels per warp)
+template <int EW>
+__global__ void __launch_bounds__(EW * 32 + 64, 1)
 conv2_fwd_tc3_kernel(const __grid_constant__ CUtensorMap mapP, const __grid_constant__ CUtensorMap mapW,
                      const float* __restrict__ bias, const B200Ctrl* __restrict__ ctrl, float* __restrict__ pooled,
                      uint8_t* __restrict__ amax, int nitems, int dbg) {
@@ -258,7 +282,7 @@ conv2_fwd_tc3_kernel(const __grid_constant__ CUtensorMap mapP, const __grid_cons
     mbar_init(&w_bar, 1);
     for (int i = 0; i < 2; ++i) {
       mbar_init(&pfull[i], 1); mbar_init(&pempty[i], 1);
-      mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 8);
+      mbar_init(&tfull[i], 1); mbar_init(&tempty[i], EW);
     }
     fence_barrier_init();
   }
@@ -312,7 +336,8 @@ conv2_fwd_tc3_kernel(const __grid_constant__ CUtensorMap mapP, const __grid_cons
       if (leader) umma_commit(&pempty[buf]);
     }
   } else {
-    // 8 epilogue warps: warp pairs (w, w+4) share a TMEM sub-partition; each takes 32 of the 64 channels
+    // warps w, w+4, .. share a TMEM sub-partition; each takes NCH of the 64 channels
+    constexpr int NCH = 256 / EW;
     const int q = wq, oc = (warp - 2) >> 2;
     const int train = ctrl->train;
     const unsigned long long seed = ctrl->seed, step = ctrl->step;
@@ -329,18 +354,24 @@ conv2_fwd_tc3_kernel(const __grid_constant__ CUtensorMap mapP, const __grid_cons
         const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + slot * 256;
         const int ph = ty * 4 + q, pw = (X0 + lx) >> 1;
         const uint32_t e_pixel = ((uint32_t)(n * HP + ph) * WP + pw) * C2;
-        float v0[32], v1[32], v2[32];
-        tmem_ld32(taddr + oc * 32, v0);        // kw = 0
-        tmem_ld32(taddr + 64 + oc * 32, v1);   // kw = 1
-        tmem_ld32(taddr + 128 + oc * 32, v2);  // kw = 2
+        float v0[NCH], v1[NCH], v2[NCH];
+        if (NCH == 32) {
+          tmem_ld32(taddr + oc * 32, reinterpret_cast<float(&)[32]>(v0));        // kw = 0
+          tmem_ld32(taddr + 64 + oc * 32, reinterpret_cast<float(&)[32]>(v1));   // kw = 1
+          tmem_ld32(taddr + 128 + oc * 32, reinterpret_cast<float(&)[32]>(v2));  // kw = 2
+        } else {
+          tmem_ld16(taddr + oc * 16, reinterpret_cast<float(&)[16]>(v0));
+          tmem_ld16(taddr + 64 + oc * 16, reinterpret_cast<float(&)[16]>(v1));
+          tmem_ld16(taddr + 128 + oc * 16, reinterpret_cast<float(&)[16]>(v2));
+        }
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&tempty[slot]);
         if (dbg & 1) continue;
 #pragma unroll
-        for (int j = 0; j < 32; ++j)
+        for (int j = 0; j < NCH; ++j)
           v0[j] += __shfl_down_sync(0xffffffffu, v1[j], 1) + __shfl_down_sync(0xffffffffu, v2[j], 2);
-        pool32_store(v0, lane, oc, bias_s, train, seed, step, e_pixel, store, pooled, amax);
+        pool_store<NCH>(v0, lane, oc, bias_s, train, seed, step, e_pixel, store, pooled, amax);
       }
     }
   }
@@ -404,8 +435,9 @@ extern "C" int b200_conv2_dgrad_tc3(const float* dy, const float* w, const float
   }
   const int nitems = 2 * batch;
   const int grid = min(nitems, b200_sm_count());
+  static const int flags = getenv("B200_DG_FLAGS") ? atoi(getenv("B200_DG_FLAGS")) : 3;  // 1 balance items, 2 prefetch mask
   B200_CHECK(b200_launch(conv2_dgrad_tc3_kernel, dim3(grid), dim3(320), (size_t)DG_SMEM, (cudaStream_t)stream, md, mw, a1,
-                         da1, nitems));
+                         da1, nitems, flags));
   b200_count_launch();
   B200_LAUNCH_CHECK();
   return B200_OK;
@@ -421,13 +453,20 @@ extern "C" int b200_conv2_fwd_tc3(const float* a1, const float* w, const float* 
   if (r != B200_OK) return r;
   static bool attr = false;
   if (!attr) {
-    B200_CHECK(cudaFuncSetAttribute(conv2_fwd_tc3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, F3_SMEM));
+    B200_CHECK(cudaFuncSetAttribute(conv2_fwd_tc3_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, F3_SMEM));
+    B200_CHECK(cudaFuncSetAttribute(conv2_fwd_tc3_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, F3_SMEM));
     attr = true;
   }
   const int nitems = 2 * batch;
   const int grid = min(nitems, b200_sm_count());
-  B200_CHECK(b200_launch(conv2_fwd_tc3_kernel, dim3(grid), dim3(320), (size_t)F3_SMEM, (cudaStream_t)stream, mp, mw, bias,
-                         (const B200Ctrl*)ctrl, pooled, amax, nitems, getenv("B200_DBG") ? atoi(getenv("B200_DBG")) : 0));
+  static const int ew = getenv("B200_FWD_EW") ? atoi(getenv("B200_FWD_EW")) : 16;
+  static const int dbg = getenv("B200_DBG") ? atoi(getenv("B200_DBG")) : 0;
+  if (ew == 8)
+    B200_CHECK(b200_launch(conv2_fwd_tc3_kernel<8>, dim3(grid), dim3(320), (size_t)F3_SMEM, (cudaStream_t)stream, mp, mw, bias,
+                           (const B200Ctrl*)ctrl, pooled, amax, nitems, dbg));
+  else
+    B200_CHECK(b200_launch(conv2_fwd_tc3_kernel<16>, dim3(grid), dim3(576), (size_t)F3_SMEM, (cudaStream_t)stream, mp, mw, bias,
+                           (const B200Ctrl*)ctrl, pooled, amax, nitems, dbg));
   b200_count_launch();
   B200_LAUNCH_CHECK();
   return B200_OK;

@@ -65,7 +65,7 @@ constexpr int BM = 128, BK = 32, STAGES = 4;
 constexpr int A_BYTES = BM * BK * 4;  // 16 KiB
 
 template <int BN, bool A_MN, bool B_MN, int EPI>
-__global__ void __launch_bounds__(192, 1)
+__global__ void __launch_bounds__(EPI == 2 ? 192 : 320, 1)
 tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
                float* __restrict__ D, int M, int N, int nkb_total, int kb_per_split, const float* __restrict__ aux,
                float scale, const uint8_t* __restrict__ amax, float* __restrict__ dy, float* __restrict__ db_part) {
@@ -141,16 +141,36 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
       if (leader) umma_commit(&tmem_full_bar);
     }
   } else {
+    // 4 epilogue warps (EPI 2) or 8: warps w and w+4 share TMEM sub-partition q and take alternate
+    // 32-column chunks of the tile
     const int q = wq;  // TMEM sub-partition this warp may read
-    mbar_wait(&tmem_full_bar, 0);
-    tc_fence_after();
+    const int h = (warp - 2) >> 2, cstep = 32 * ((nwarps - 2) >> 2);
     const int m = m0 + q * 32 + lane;
     float* drow = D + ((size_t)blockIdx.z * M + m) * N;
     const float* arow = EPI == 1 ? aux + (size_t)m * N : nullptr;
+    // EPI 1: the mask operand does not depend on the MMAs; its (row-strided, slow) loads are issued one
+    // chunk ahead, the first of them before the accumulator is waited for
+    float4 anext[8];
+    auto load_aux = [&](int c0) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int n = n0 + c0 + 4 * j;
+        anext[j] = (m < M && n < N) ? *reinterpret_cast<const float4*>(arow + n) : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+    };
+    if (EPI == 1) load_aux(h * 32);
+    mbar_wait(&tmem_full_bar, 0);
+    tc_fence_after();
 #pragma unroll 1
-    for (int c0 = 0; c0 < BN; c0 += 32) {
+    for (int c0 = h * 32; c0 < BN; c0 += cstep) {
       float v[32];
       tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + c0, v);
+      float4 acur[8];
+      if (EPI == 1) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acur[j] = anext[j];
+        if (c0 + cstep < BN) load_aux(c0 + cstep);
+      }
       if (EPI == 2) {
         // fc1 dgrad fused with the dropout/ReLU mask, the max-pool scatter and conv2's bias gradient.
         // Columns n0+c0 .. +31 are 32 consecutive channels of ONE pooled pixel.  The chunk is transposed
@@ -188,7 +208,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
           if (n < N) {
             float4 o = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
             if (EPI == 1) {
-              const float4 a = *reinterpret_cast<const float4*>(arow + n);
+              const float4 a = acur[j >> 2];
               o.x = a.x > 0.f ? o.x * scale : 0.f; o.y = a.y > 0.f ? o.y * scale : 0.f;
               o.z = a.z > 0.f ? o.z * scale : 0.f; o.w = a.w > 0.f ? o.w * scale : 0.f;
             }
@@ -252,7 +272,8 @@ int launch(const CUtensorMap& ma, const CUtensorMap& mb, float* D, int M, int N,
     attr = true;
   }
   dim3 grid(ceil_div(N, BN), ceil_div(M, BM), splits);
-  B200_CHECK(b200_launch(tc_gemm_kernel<BN, A_MN, B_MN, EPI>, grid, dim3(192), (size_t)smem, s, ma, mb, D, M, N, nkb, kbs,
+  static const int ew = getenv("B200_GEMM_EW") ? atoi(getenv("B200_GEMM_EW")) : 8;  // epilogue warps: 4 or 8
+  B200_CHECK(b200_launch(tc_gemm_kernel<BN, A_MN, B_MN, EPI>, grid, dim3(EPI == 2 || ew == 4 ? 192 : 320), (size_t)smem, s, ma, mb, D, M, N, nkb, kbs,
                          aux, scale, amax, dy, db_part));
   b200_count_launch();
   B200_LAUNCH_CHECK();

@@ -1,0 +1,48 @@
+// Does a small kernel co-reside with a persistent kernel that holds most of the SM's shared memory?
+#include <cstdio>
+#include <cmath>
+#include <cuda_runtime.h>
+__global__ void __launch_bounds__(320, 1) big(unsigned long long ns, int* sink) {
+  extern __shared__ unsigned char sm[];
+  unsigned long long t0, t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+  do { asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); } while (t - t0 < ns);
+  if (sink && threadIdx.x == 0 && ns == 1 && sm[0] == 77) *sink = 1;
+}
+__global__ void small(float* p, int n, unsigned long long* stamp) {
+  unsigned long long t;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) p[i] = p[i] * 1.0001f + 1.f;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  if (threadIdx.x == 0) atomicMax(stamp, t);
+}
+__global__ void stamp_k(unsigned long long* s) { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); *s = t; }
+int main() {
+  float* p; cudaMalloc(&p, 16 << 20); cudaMemset(p, 0, 16 << 20);
+  unsigned long long* st; cudaMallocManaged(&st, 64);
+  int* sink; cudaMalloc(&sink, 4);
+  cudaStream_t s1, s2; cudaStreamCreateWithFlags(&s1, cudaStreamNonBlocking); cudaStreamCreateWithFlags(&s2, cudaStreamNonBlocking);
+  cudaFuncSetAttribute(big, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+  int smems[] = {222208, 214016, 200 * 1024, 160 * 1024, 100 * 1024, 16 * 1024};
+  for (int carve = 0; carve < 2; ++carve) {
+    if (carve) cudaFuncSetAttribute(small, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    for (int smem : smems) {
+      double best = 1e9;
+      for (int rep = 0; rep < 6; ++rep) {
+        st[0] = st[1] = 0;
+        cudaDeviceSynchronize();
+        stamp_k<<<1, 1, 0, s1>>>(st);
+        big<<<148, 320, smem, s1>>>(100000ull, sink);
+        cudaEvent_t e; cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
+        cudaEventRecord(e, s1);  // after big is *enqueued*; wait only on the stamp via a separate event is not possible, so:
+        small<<<592, 256, 0, s2>>>(p, 1 << 20, st + 1);
+        cudaDeviceSynchronize();
+        if (rep) best = fmin(best, (double)(st[1] - st[0]) / 1000.0);
+        if (rep == 5) printf("carveout_max=%d big_smem=%6d : small finished %.1f us after start (big spins 100 us)\n", carve, smem,
+                        best);
+        cudaEventDestroy(e);
+      }
+    }
+  }
+  printf("%s\n", cudaGetErrorString(cudaGetLastError()));
+  return 0;
+}
