@@ -173,20 +173,22 @@ int enqueue_train(Engine* E, const uint8_t* images, const uint8_t* labels, const
   bool fc_updated = false;
   if (par) {
     B200_CHECK(cudaEventRecord(E->ev_fcw, sw));
-    if (own_update) {
-      // single GPU: the fc bucket (98 % of the parameters) gets its Adadelta update on the branch, under
-      // the conv backward; it may only start once fc1 dgrad has read the old fc1.weight
+    if (E->defer_update) {
+      B200_CHECK(cudaStreamWaitEvent(s, E->ev_fcw, 0));  // the caller reduces/updates: the fc bucket must be complete
+    } else {
+      // The fc bucket (98 % of the parameters) is complete on the branch.  Its update -- Adadelta on one
+      // GPU, the fused all-reduce + Adadelta kernel with data parallelism -- stays on the branch, under
+      // the conv backward; it may only start once fc1 dgrad has read the old fc1.weight.
       B200_CHECK(cudaEventRecord(E->ev_fcd, s));
       B200_CHECK(cudaStreamWaitEvent(sw, E->ev_fcd, 0));
-      TRYM(b200_adadelta(P, G, E->V, E->U, c.bucket_begin[1], E->ctrl, 0.9f, 1e-6f, -1, nullptr, sw), sw);
+      if (own_update) TRYM(b200_adadelta(P, G, E->V, E->U, c.bucket_begin[1], E->ctrl, 0.9f, 1e-6f, -1, nullptr, sw), sw);
+      else TRYM(E->hooks.bucket_ready(E, 0, sw), sw);
       B200_CHECK(cudaEventRecord(E->ev_fcu, sw));
       fc_updated = true;
-    } else {
-      B200_CHECK(cudaStreamWaitEvent(s, E->ev_fcw, 0));  // the bucket hook / the caller needs the whole fc bucket
     }
+  } else if (E->hooks.bucket_ready) {
+    TRYM(E->hooks.bucket_ready(E, 0, s), s);  // bucket 0 (fc1.*, fc2.*) is complete here
   }
-  // bucket 0 (fc1.*, fc2.*) is complete here
-  if (E->hooks.bucket_ready) TRYM(E->hooks.bucket_ready(E, 0, s), s);
   // With data-parallel hooks the conv-bucket gradients are left as per-CTA partials: the step's last
   // kernel reduces them, all-reduces, and applies Adadelta in one go (fin).
   const bool fuse = E->hooks.bucket_ready != nullptr || !E->defer_update;
