@@ -17,6 +17,8 @@ __global__ void __launch_bounds__(256)
 adadelta_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ v, float* __restrict__ u,
                 int n4, B200Ctrl* __restrict__ ctrl, float rho, float eps, int advance_batch,
                 unsigned int* __restrict__ done_counter) {
+  pdl_trigger();
+  pdl_wait();
   const float lr = ctrl->lr;
   for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < n4; e += gridDim.x * blockDim.x) {
     const float4 gg = reinterpret_cast<const float4*>(g)[e];

@@ -343,7 +343,7 @@ int hook_bucket_ready(Engine* E, int bucket, cudaStream_t s) {
     B200_CHECK(cudaStreamWaitEvent(d->comm, d->fork, 0));
     // Footprint of the side-stream reducer (env-tunable).  Measured at W = 2 (us/step): 64x512 160.8,
     // 37x512 167, 148x512 174, 74x256 172, 148x256 186, 148x128 206 — few fat CTAs beat one light CTA per SM.
-    static const int nb0 = getenv("B200_DDP_B0_BLOCKS") ? atoi(getenv("B200_DDP_B0_BLOCKS")) : 64;
+    static const int nb0 = getenv("B200_DDP_B0_BLOCKS") ? atoi(getenv("B200_DDP_B0_BLOCKS")) : 96;
     static const int th0 = getenv("B200_DDP_B0_THREADS") ? atoi(getenv("B200_DDP_B0_THREADS")) : 512;
     int r = run_plan(d->plan[0], d->mode[0], 1, 0, min(nb0, SYMM_MAX_BLOCKS), 0.9f, 1e-6f, d->comm, -1, nullptr, exit_b, th0);
     if (r != B200_OK) return r;

@@ -41,7 +41,7 @@ int b200_sm_count();
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 #endif
-bool b200_pdl_enabled();  // runtime.cu: experimental, only with B200_PDL=1 (see the note there)
+bool b200_pdl_enabled(const void* kernel);  // runtime.cu: experimental, only with B200_PDL=1 (see the note there)
 
 // Every kernel of the step asks for the maximum shared-memory carve-out, also those that use little or
 // no shared memory.  An SM only runs CTAs of kernels with the same L1/shared split at the same time, and
@@ -50,8 +50,8 @@ bool b200_pdl_enabled();  // runtime.cu: experimental, only with B200_PDL=1 (see
 void b200_prefer_max_shared(const void* kernel);  // runtime.cu; once per kernel
 
 template <typename... KArgs, typename... Args>
-inline cudaError_t b200_launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s,
-                               Args&&... args) {
+inline cudaError_t b200_launch_ex(bool allow_pdl, void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem,
+                                  cudaStream_t s, Args&&... args) {
   b200_prefer_max_shared((const void*)kernel);
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = grid;
@@ -62,8 +62,20 @@ inline cudaError_t b200_launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, 
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = b200_pdl_enabled() ? 1 : 0;
+  cfg.numAttrs = (allow_pdl && b200_pdl_enabled((const void*)kernel)) ? 1 : 0;
   return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+template <typename... KArgs, typename... Args>
+inline cudaError_t b200_launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s,
+                               Args&&... args) {
+  return b200_launch_ex(true, kernel, grid, block, smem, s, static_cast<Args&&>(args)...);
+}
+// for the first kernel of a step: it follows copies, other streams' joins and the previous step's end
+// marker, and is always launched with full stream serialisation
+template <typename... KArgs, typename... Args>
+inline cudaError_t b200_launch_serial(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s,
+                                      Args&&... args) {
+  return b200_launch_ex(false, kernel, grid, block, smem, s, static_cast<Args&&>(args)...);
 }
 
 // ---- second-level reduction of per-CTA partial rows, inside the producing kernel ---------------------

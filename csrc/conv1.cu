@@ -162,7 +162,7 @@ void b200_launch_reduce_partials(float* dst, const float* src, int n, int nparts
 extern "C" int b200_conv1_fwd(const uint8_t* images, const int32_t* idx, const void* ctrl, const float* w,
                               const float* bias, float* a1, int batch, void* stream) {
   B200_REQUIRE(batch > 0, "conv1_fwd: batch must be > 0");
-  B200_CHECK(b200_launch(conv1_fwd_kernel, dim3(batch), dim3(256), 0, (cudaStream_t)stream, images, idx,
+  B200_CHECK(b200_launch_serial(conv1_fwd_kernel, dim3(batch), dim3(256), 0, (cudaStream_t)stream, images, idx,
                          (const B200Ctrl*)ctrl, w, bias, a1));
   b200_count_launch();
   B200_LAUNCH_CHECK();

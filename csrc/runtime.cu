@@ -5,6 +5,7 @@
 #include <cstring>
 #include <mutex>
 #include <unordered_set>
+#include <vector>
 
 #include "common.cuh"
 
@@ -20,11 +21,20 @@ void b200_set_error(const char* fmt, ...) {
 
 void b200_count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 
-bool b200_pdl_enabled() {
-  // Off by default: measured on B200 the early-scheduled dependents cost more (147 vs 137 us/step) than
-  // the hidden launch latency saves, and graph replay was no longer bit-identical to eager launches.
+bool b200_pdl_enabled(const void* kernel) {
+  // B200_PDL=1 turns programmatic dependent launch on; B200_PDL_MASK (diagnostics) limits it to the kernels
+  // whose first-launch index has its bit set.
   static const bool on = getenv("B200_PDL") && atoi(getenv("B200_PDL")) == 1;
-  return on;
+  if (!on) return false;
+  static const long mask = getenv("B200_PDL_MASK") ? strtol(getenv("B200_PDL_MASK"), nullptr, 0) : -1;
+  if (mask == -1) return true;
+  static std::mutex mu;
+  static std::vector<const void*> order;
+  std::lock_guard<std::mutex> lock(mu);
+  size_t i = 0;
+  for (; i < order.size(); ++i) if (order[i] == kernel) break;
+  if (i == order.size()) order.push_back(kernel);
+  return i < 63 && ((mask >> i) & 1);
 }
 
 void b200_prefer_max_shared(const void* kernel) {

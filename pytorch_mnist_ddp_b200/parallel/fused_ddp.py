@@ -15,8 +15,8 @@ is rebuilt here on top of csrc/symm.cu and csrc/allreduce.cu:
   the end (SURVEY N17 bucket layout; section 8 rows 11, 12, 15).
 
 Reduction modes (``--comm``): ``oneshot`` (every rank reduces the whole bucket), ``twoshot``
-(reduce-scatter + sharded Adadelta + parameter all-gather), ``auto`` = two-shot for the 4.7 MB fc
-bucket when world >= 4, one-shot otherwise; ``nvls`` = two-shot through the NVSwitch
+(reduce-scatter + sharded Adadelta + parameter all-gather), ``auto`` = ``nvls`` for the 4.7 MB fc
+bucket when the arena gets a multicast mapping, two-shot otherwise; ``nvls`` = two-shot through the NVSwitch
 (``multimem.ld_reduce`` + ``multimem.st`` on a multicast mapping from torch symmetric memory).  ``nccl`` keeps the reference's unfused structure
 (ncclAllReduce + separate Adadelta) as the in-tree baseline.
 """
@@ -161,15 +161,15 @@ class FusedDataParallel:
             raise ValueError(f"unknown comm mode {comm}")
         self.info, self.comm = info, comm
         w = info.world_size
-        if comm == "auto":
-            self.modes = (TWOSHOT if w >= 4 else ONESHOT, ONESHOT)
+        if comm == "auto":  # resolved in allocate(): NVLS when the arena gets a multicast mapping, else two-shot
+            self.modes = (TWOSHOT, ONESHOT)
         elif comm == "twoshot":
             self.modes = (TWOSHOT, ONESHOT)
         elif comm == "nvls":  # fc bucket through the switch (multimem), conv bucket one-shot P2P
             self.modes = (NVLS, ONESHOT)
         else:
             self.modes = (ONESHOT, ONESHOT)
-        self.mode = {"auto": f"auto({'twoshot' if self.modes[0] else 'oneshot'}+oneshot)"}.get(comm, comm)
+        self.mode = comm
         self.arena: Optional[SymmetricArena] = None
         self.total = 0
 
@@ -180,6 +180,27 @@ class FusedDataParallel:
             self.arena = SymmetricArena.create_torch(self.info, 4 * total_floats)
             if not getattr(self.arena, "has_multicast", False):
                 raise N.NativeError("--comm nvls: this host/driver gave no multicast mapping (NVLS unavailable)")
+        elif self.comm == "auto":
+            # Measured on B200 (2 GPUs, us/step): NVLS 140.9, two-shot 142-151, one-shot 149-157.  Every rank
+            # must take the same branch, so the outcome of the multicast probe is agreed on with an all-reduce.
+            arena = None
+            try:
+                arena = SymmetricArena.create_torch(self.info, 4 * total_floats)
+                ok = 1 if getattr(arena, "has_multicast", False) else 0
+            except Exception:
+                ok = 0
+            flag = torch.tensor([ok], device="cuda", dtype=torch.int32)
+            if dist.is_initialized():
+                dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+            if int(flag.item()) == 1:
+                self.arena = arena
+                self.modes = (NVLS, ONESHOT)
+                self.mode = "auto(nvls+oneshot)"
+            else:
+                if arena is not None:
+                    arena.destroy()
+                self.arena = SymmetricArena.create(self.info, 4 * total_floats)
+                self.mode = "auto(twoshot+oneshot)"
         else:
             self.arena = SymmetricArena.create(self.info, 4 * total_floats)
         base = self.arena.base_ptr()

@@ -103,7 +103,7 @@ def _torchrun(nproc, script_args, timeout=600):
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs >= 2 GPUs")
-@pytest.mark.parametrize("comm", ["oneshot", "twoshot", "nvls"])
+@pytest.mark.parametrize("comm", ["oneshot", "twoshot", "nvls", "auto"])
 def test_multi_gpu_ddp_equivalence(comm):
     """2 ranks x batch b without dropout == 1 rank x batch 2b ('DDP equivalence')."""
     res = _torchrun(2, ["tests/ddp_worker.py", "--comm", comm])
