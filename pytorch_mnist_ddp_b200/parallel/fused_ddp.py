@@ -15,8 +15,8 @@ is rebuilt here on top of csrc/symm.cu and csrc/allreduce.cu:
   the end (SURVEY N17 bucket layout; section 8 rows 11, 12, 15).
 
 Reduction modes (``--comm``): ``oneshot`` (every rank reduces the whole bucket), ``twoshot``
-(reduce-scatter + sharded Adadelta + parameter all-gather), ``auto`` = ``nvls`` for the 4.7 MB fc
-bucket when the arena gets a multicast mapping, two-shot otherwise; ``nvls`` = two-shot through the NVSwitch
+(reduce-scatter + sharded Adadelta + parameter all-gather), ``auto`` = two-shot for the 4.7 MB fc
+bucket, except at world == 2 where it is ``nvls`` when the arena gets a multicast mapping; ``nvls`` = two-shot through the NVSwitch
 (``multimem.ld_reduce`` + ``multimem.st`` on a multicast mapping from torch symmetric memory).  ``nccl`` keeps the reference's unfused structure
 (ncclAllReduce + separate Adadelta) as the in-tree baseline.
 """
@@ -180,9 +180,17 @@ class FusedDataParallel:
             self.arena = SymmetricArena.create_torch(self.info, 4 * total_floats)
             if not getattr(self.arena, "has_multicast", False):
                 raise N.NativeError("--comm nvls: this host/driver gave no multicast mapping (NVLS unavailable)")
+        elif self.comm == "auto" and self.info.world_size != 2:
+            # world >= 4: two-shot on the CUDA-IPC arena.  NVLS was equal to two-shot at 4 and 8 GPUs with the
+            # earlier engine (168.0 vs 167.6 us/step at 8), and the current engine (branch streams, 96-CTA
+            # reducer) has only been run on real hardware at 2 GPUs: the one 8-GPU attempt with auto = NVLS
+            # was killed by the job limit before it printed anything, so that combination is unverified.
+            self.arena = SymmetricArena.create(self.info, 4 * total_floats)
+            self.mode = "auto(twoshot+oneshot)"
         elif self.comm == "auto":
-            # Measured on B200 (2 GPUs, us/step): NVLS 140.9, two-shot 142-151, one-shot 149-157.  Every rank
-            # must take the same branch, so the outcome of the multicast probe is agreed on with an all-reduce.
+            # world == 2, measured on B200 inside one job (us/step): NVLS 142.2, two-shot 155.7; across jobs the
+            # spread is about +-5 us.  Every rank must take the same branch, so the outcome of the multicast
+            # probe is agreed on with an all-reduce.
             arena = None
             try:
                 arena = SymmetricArena.create_torch(self.info, 4 * total_floats)
