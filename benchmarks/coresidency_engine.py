@@ -1,6 +1,6 @@
 # Does adadelta (SIMT, no smem) co-reside with the persistent conv kernels when launched while they run?
 import sys, torch
-sys.path.insert(0, "/root/repo")
+sys.path.insert(0, __import__("os").path.dirname(__import__("os").path.dirname(__import__("os").path.abspath(__file__))))
 from pytorch_mnist_ddp_b200 import _native as N
 from pytorch_mnist_ddp_b200.ops import native_ops as ops
 L = N.lib()

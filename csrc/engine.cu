@@ -7,15 +7,20 @@
 // device-driven: sample cursor, step counter (dropout offset), lr and the loss ring live in a
 // device control block, so the host only enqueues "one more step" and never synchronises.
 //
-// Kernel sequence of a step (single GPU, resident data):
+// Kernels of a step (single GPU, resident data).  Main stream = the critical path:
 //   conv1_fwd (gather+normalise+conv+ReLU) -> conv2_fwd (+bias+ReLU+pool+dropout)
 //   -> fc1 GEMM (split-K) -> head_fused (reduce+bias+ReLU+dropout, fc2, log_softmax, NLL, bwd seed)
-//   -> head_wgrad -> fc1 wgrad -> fc1 dgrad (+dropout/ReLU mask) -> [bucket 0 ready]
-//   -> conv2 wgrad -> conv2 dgrad (+ReLU mask) -> conv1 wgrad -> [bucket 1 ready] -> Adadelta.
-// With world > 1 the "bucket ready" points launch the fused all-reduce+Adadelta kernels of
-// allreduce.cu on a second stream (bucket 0 overlaps the conv backward) instead of the local
-// Adadelta.  Gradients are written straight into the flat (symmetric) bucket: there is no
-// bucket copy-in/copy-out and no zero_grad (every wgrad kernel overwrites).
+//   -> fc1 dgrad (+dropout/ReLU mask) -> un-pool -> conv2 dgrad (+ReLU mask) -> conv1 wgrad
+//   -> last kernel: conv-bucket partial reduction + Adadelta + step counter advance.
+// Branch 0 (forked after head_fused): head_wgrad -> fc1 wgrad -> [bucket 0 ready] fc-bucket Adadelta
+//   (waits for fc1 dgrad, which still reads the old fc1.weight).
+// Branch 1 (forked after un-pool): conv2 wgrad.
+// Both branches are joined before the last kernel; forks and joins are events, so the whole step is
+// still ONE capturable graph.  With world > 1 the "bucket ready" point launches the fused
+// all-reduce+Adadelta kernel of allreduce.cu from branch 0 (it overlaps the conv backward) and the last
+// kernel is allreduce.cu's finalize_bucket_kernel.  Gradients are written straight into the flat
+// (symmetric) bucket: there is no bucket copy-in/copy-out and no zero_grad (every wgrad
+// kernel overwrites).
 #include <cstdlib>
 #include <cstring>
 #include <map>
