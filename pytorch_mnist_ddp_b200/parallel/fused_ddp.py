@@ -161,7 +161,7 @@ class FusedDataParallel:
             raise ValueError(f"unknown comm mode {comm}")
         self.info, self.comm = info, comm
         w = info.world_size
-        if comm == "auto":  # resolved in allocate(): NVLS when the arena gets a multicast mapping, else two-shot
+        if comm == "auto":  # resolved in allocate(): two-shot, or NVLS at world == 2 when a multicast mapping exists
             self.modes = (TWOSHOT, ONESHOT)
         elif comm == "twoshot":
             self.modes = (TWOSHOT, ONESHOT)
