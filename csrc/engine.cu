@@ -203,13 +203,21 @@ int enqueue_train(Engine* E, const uint8_t* images, const uint8_t* labels, const
   int np2 = 0;
   bool c2w_pending = false;
   if (E->use_tc & B200_TC_CONV2_BWD) {
-    if (!fuse_unpool) {
-      if (fuse) TRYM(b200_unpool_dense_grouped(E->dp, E->amax, E->dy, E->db_part, E->db_gpart, E->db_cnt, batch, s), s);
-      else TRYM(b200_unpool_dense(E->dp, E->amax, E->dy, E->db_part, db2, batch, s), s);
-    }
+    // Draft path (B200_TC bit 64, off by default): the v4 dgrad expands (dp, amax) itself, so only conv2 wgrad
+    // still needs the dense dY and the un-pool kernel moves to the wgrad branch, off the critical path.
+    const bool v4 = (E->use_tc & B200_TC_CONV2_V4) && (E->use_tc & B200_TC_CONV2_V2) && !fuse_unpool;
     // Fork: conv2 wgrad and conv2 dgrad both read dY; wgrad runs beside dgrad / conv1 wgrad
     cudaStream_t sc = par ? E->br[1] : s;
-    if (par) {
+    cudaStream_t su = (v4 && par) ? sc : s;  // stream of the un-pool kernel
+    if (par && v4) {
+      B200_CHECK(cudaEventRecord(E->ev_dy, s));
+      B200_CHECK(cudaStreamWaitEvent(sc, E->ev_dy, 0));
+    }
+    if (!fuse_unpool) {
+      if (fuse) TRYM(b200_unpool_dense_grouped(E->dp, E->amax, E->dy, E->db_part, E->db_gpart, E->db_cnt, batch, su), su);
+      else TRYM(b200_unpool_dense(E->dp, E->amax, E->dy, E->db_part, db2, batch, su), su);
+    }
+    if (par && !v4) {
       B200_CHECK(cudaEventRecord(E->ev_dy, s));
       B200_CHECK(cudaStreamWaitEvent(sc, E->ev_dy, 0));
     }
@@ -218,6 +226,7 @@ int enqueue_train(Engine* E, const uint8_t* images, const uint8_t* labels, const
       const bool do_wgrad = (pass == 0) != par;
       if (E->use_tc & B200_TC_CONV2_V2) {
         if (do_wgrad) TRYM(b200_conv2_wgrad_tc2(E->dy, E->a1, E->c2_part, dw2, batch, sc), sc);
+        else if (v4) TRYM(b200_conv2_dgrad_tc4(E->dp, E->amax, P + c.offsets[2], E->a1, E->da1, batch, s), s);
         else if (E->use_tc & B200_TC_CONV2_V3) TRYM(b200_conv2_dgrad_tc3(E->dy, P + c.offsets[2], E->a1, E->da1, batch, s), s);
         else TRYM(b200_conv2_dgrad_tc2(E->dy, P + c.offsets[2], E->a1, E->da1, batch, s), s);
       } else {

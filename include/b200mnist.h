@@ -95,6 +95,10 @@ int b200_conv2_fwd_tc3(const float* a1, const float* w, const float* bias, const
                        uint8_t* amax, int batch, void* stream);
 /* third generation dgrad: the three kw taps sit on the N side of the MMA (128x96x8), summed by shuffles */
 int b200_conv2_dgrad_tc3(const float* dy, const float* w, const float* a1, float* da1, int batch, void* stream);
+/* DRAFT (compiles, not yet validated on a GPU, never selected by default): conv2 dgrad that expands the pooled
+ * gradient dp[B][12][12][64] + arg-max codes in its producer warps instead of reading a dense dY tensor. */
+int b200_conv2_dgrad_tc4(const float* dp, const uint8_t* amax, const float* w, const float* a1, float* da1, int batch,
+                         void* stream);
 int b200_conv2_wgrad_tc2(const float* dy, const float* a1, float* part, float* dw, int batch, void* stream);
 /* implicit-GEMM dgrad from the dense dY [B][24][24][64]; epilogue applies conv1's ReLU mask */
 int b200_conv2_dgrad_tc(const float* dy, const float* w, const float* a1, float* da1, int batch, void* stream);

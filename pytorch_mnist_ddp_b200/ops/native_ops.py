@@ -93,6 +93,9 @@ def fc1_dgrad_unpool(dh: torch.Tensor, w1: torch.Tensor, pooled: torch.Tensor, a
 def conv2_dgrad(dp, amax, w, a1, tc: bool = False) -> torch.Tensor:
     batch = dp.shape[0]
     da1 = torch.empty(batch, 26, 26, 32, device="cuda")
+    if tc == 4:  # draft kernel: expands (dp, amax) itself, no dense dY
+        N.check(N.lib().b200_conv2_dgrad_tc4(_p(dp), _p(amax), _p(w), _p(a1), _p(da1), batch, _s()))
+        return da1
     if tc:
         dy = unpool_dense(dp, amax)
         L = N.lib()

@@ -4,6 +4,8 @@ Oracle = torch ops on the GPU with TF32 disabled (the reference trains convs in 
 fp32; the CUDA-core kernels here are full fp32, the tcgen05 ones TF32 — tolerances
 below reflect that).  Layout conversions are done here, never in the kernels under test.
 """
+import os
+
 import pytest
 import torch
 import torch.nn.functional as F
@@ -220,6 +222,23 @@ def test_conv2_backward(ops, batch, tc):
     assert rel(db, net.conv2.bias.grad) < 2e-3, rel(db, net.conv2.bias.grad)
     assert rel(da1, ref_da1) < lim, rel(da1, ref_da1)
     assert (da1[a1 <= 0] == 0).all(), "ReLU mask of conv1 must be applied"
+
+
+@pytest.mark.skipif(os.environ.get("B200_DRAFT") != "1",
+                    reason="draft kernel (tc_conv2_v4.cu) has never run on a GPU yet; set B200_DRAFT=1 to try it")
+@pytest.mark.parametrize("batch", [1, 7, 64, 200])
+def test_conv2_dgrad_draft_v4_equals_v3(ops, batch):
+    """The dY-free dgrad must reproduce the v3 kernel (same MMAs, different producer) bit for bit."""
+    _need_tc(True)
+    net = _net()
+    w = _internal(net)
+    a1 = (torch.rand(batch, 26, 26, 32, device="cuda") - 0.3).clamp_min(0)
+    pooled, amax = ops.conv2_fwd(a1, w["conv2.weight"], w["conv2.bias"], ops.make_ctrl(train=False))
+    dp = torch.randn(batch, 12, 12, 64, device="cuda") * (pooled > 0)
+    ref = ops.conv2_dgrad(dp, amax, w["conv2.weight"], a1, tc=3)
+    got = ops.conv2_dgrad(dp, amax, w["conv2.weight"], a1, tc=4)
+    torch.cuda.synchronize()
+    assert torch.equal(ref, got), (ref - got).abs().max().item()
 
 
 @pytest.mark.parametrize("batch", [1, 7, 64])
