@@ -43,7 +43,10 @@ void b200_prefer_max_shared(const void* kernel) {
   std::lock_guard<std::mutex> lock(mu);
   if (!seen.insert(kernel).second) return;
   static const bool off = getenv("B200_NO_CARVEOUT") != nullptr;  // diagnostics
-  if (!off) cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+  // only a scheduling hint: a refusal must not surface as a launch error later
+  if (!off && cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                   cudaSharedmemCarveoutMaxShared) != cudaSuccess)
+    cudaGetLastError();
 }
 
 int b200_sm_count() {
