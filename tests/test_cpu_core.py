@@ -238,3 +238,34 @@ def test_cpu_trajectory_is_bit_identical_to_reference_script(tmp_path):
     assert ref.returncode == 0 and ours.returncode == 0, ref.stderr[-1500:] + ours.stderr[-1500:]
     pick = lambda s: [l for l in s.splitlines() if l.startswith(("Train Epoch", "Test set"))]
     assert pick(ours.stdout) == pick(ref.stdout), (pick(ours.stdout), pick(ref.stdout))
+
+
+@pytest.mark.parametrize("branch", ["torchrun", "slurm", "preset", "none"])
+def test_init_distributed_mode_discovery_branches(branch, monkeypatch, capsys):
+    """The four discovery branches of init_distributed_mode (mnist_ddp.py:13-37), process group mocked."""
+    import argparse
+    import torch.distributed as dist
+    from pytorch_mnist_ddp_b200.parallel import dist as pdist
+    calls = {}
+    monkeypatch.setattr(dist, "init_process_group", lambda **kw: calls.update(kw))
+    for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK", "SLURM_PROCID"):
+        monkeypatch.delenv(k, raising=False)
+    args = argparse.Namespace(world_size=4, dist_url="env://", local_rank=0)
+    if branch == "torchrun":
+        monkeypatch.setenv("RANK", "3"); monkeypatch.setenv("WORLD_SIZE", "8"); monkeypatch.setenv("LOCAL_RANK", "3")
+    elif branch == "slurm":
+        monkeypatch.setenv("SLURM_PROCID", "2")
+    elif branch == "preset":
+        args.rank, args.gpu = 1, 0
+    info = pdist.init_distributed_mode(args, use_cuda=False)
+    out = capsys.readouterr().out
+    if branch == "none":
+        assert out.strip() == "Not using distributed mode" and not info.distributed and info.world_size == 1
+        assert not calls
+        return
+    want = {"torchrun": (3, 8, 3), "slurm": (2, 4, 0), "preset": (1, 4, 0)}[branch]
+    assert (info.rank, info.world_size, info.gpu) == want and info.distributed
+    assert calls["backend"] == "gloo" and calls["init_method"] == "env://"
+    assert calls["rank"] == want[0] and calls["world_size"] == want[1]
+    # banner format of mnist_ddp.py:34
+    assert out.strip() == f"| distributed init (rank {want[0]}): env://, local rank:{want[2]}, world size:{want[1]}"
