@@ -114,8 +114,15 @@ int enqueue_forward(Engine* E, const uint8_t* images, const uint8_t* labels, con
                     int batch, bool train, cudaStream_t s) {
   const B200EngineConfig& c = E->cfg;
   float* P = E->P;
-  TRYM(b200_conv1_fwd(images, idx, ctrl, P + c.offsets[0], P + c.offsets[1], E->a1, batch, s), s);
-  if ((E->use_tc & B200_TC_CONV2_FWD) && (E->use_tc & B200_TC_CONV2_V3))
+  // draft path (B200_TC bit 128, off by default): conv1 inside conv2's producer warps, one kernel for both
+  const bool fused12 = (E->use_tc & B200_TC_CONV12_V4) && (E->use_tc & B200_TC_CONV2_FWD) && (E->use_tc & B200_TC_CONV2_V3);
+  if (fused12)
+    TRYM(b200_conv12_fwd_tc4(images, idx, ctrl, P + c.offsets[0], P + c.offsets[1], E->a1, P + c.offsets[2],
+                             P + c.offsets[3], E->pooled, E->amax, batch, s), s);
+  else
+    TRYM(b200_conv1_fwd(images, idx, ctrl, P + c.offsets[0], P + c.offsets[1], E->a1, batch, s), s);
+  if (fused12) {}
+  else if ((E->use_tc & B200_TC_CONV2_FWD) && (E->use_tc & B200_TC_CONV2_V3))
     TRYM(b200_conv2_fwd_tc3(E->a1, P + c.offsets[2], P + c.offsets[3], ctrl, E->pooled, E->amax, batch, s), s);
   else if ((E->use_tc & B200_TC_CONV2_FWD) && (E->use_tc & B200_TC_CONV2_V2))
     TRYM(b200_conv2_fwd_tc2(E->a1, P + c.offsets[2], P + c.offsets[3], ctrl, E->pooled, E->amax, batch, s), s);

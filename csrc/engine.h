@@ -7,7 +7,8 @@
 #include "common.cuh"
 
 enum { B200_TC_CONV2_FWD = 1, B200_TC_FC1_FWD = 2, B200_TC_FC1_BWD = 4, B200_TC_CONV2_BWD = 8, B200_TC_CONV2_V2 = 16, B200_TC_CONV2_V3 = 32,
-       B200_TC_CONV2_V4 = 64 /* draft dY-free dgrad (tc_conv2_v4.cu), opt-in only */ };
+       B200_TC_CONV2_V4 = 64 /* draft dY-free dgrad (tc_conv2_v4.cu), opt-in only */,
+       B200_TC_CONV12_V4 = 128 /* draft fused conv1+conv2 forward (tc_conv2_v4.cu), opt-in only */ };
 
 // Where the conv bucket's gradients still sit as per-CTA partial sums at the end of backward.  The
 // last kernel of the step (allreduce.cu: finalize_bucket_kernel) reduces them itself, so no separate

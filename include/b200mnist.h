@@ -99,6 +99,11 @@ int b200_conv2_dgrad_tc3(const float* dy, const float* w, const float* a1, float
  * gradient dp[B][12][12][64] + arg-max codes in its producer warps instead of reading a dense dY tensor. */
 int b200_conv2_dgrad_tc4(const float* dp, const uint8_t* amax, const float* w, const float* a1, float* da1, int batch,
                          void* stream);
+/* DRAFT, same status: conv1 (gather + normalise + conv + bias + ReLU) computed inside conv2 forward's producer
+ * warps; a1 is still written (the backward pass reads it).  Replaces b200_conv1_fwd + b200_conv2_fwd_tc3. */
+int b200_conv12_fwd_tc4(const uint8_t* images, const int32_t* idx, const void* ctrl, const float* w1, const float* b1,
+                        float* a1, const float* w2, const float* b2, float* pooled, uint8_t* amax, int batch,
+                        void* stream);
 int b200_conv2_wgrad_tc2(const float* dy, const float* a1, float* part, float* dw, int batch, void* stream);
 /* implicit-GEMM dgrad from the dense dY [B][24][24][64]; epilogue applies conv1's ReLU mask */
 int b200_conv2_dgrad_tc(const float* dy, const float* w, const float* a1, float* da1, int batch, void* stream);

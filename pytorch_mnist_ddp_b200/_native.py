@@ -126,6 +126,7 @@ _SIGNATURES = {
     "b200_conv2_fwd_tc3": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _vp],
     "b200_conv2_dgrad_tc3": [_vp, _vp, _vp, _vp, _i, _vp],
     "b200_conv2_dgrad_tc4": [_vp, _vp, _vp, _vp, _vp, _i, _vp],
+    "b200_conv12_fwd_tc4": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp],
     "b200_conv2_wgrad_tc2": [_vp, _vp, _vp, _vp, _i, _vp],
     "b200_conv2_dgrad_tc": [_vp, _vp, _vp, _vp, _i, _vp],
     "b200_conv2_wgrad_tc": [_vp, _vp, _vp, _vp, _i, _vp],

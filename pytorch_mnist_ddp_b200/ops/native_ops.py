@@ -49,6 +49,17 @@ def conv1_fwd(images_u8: torch.Tensor, idx: Optional[torch.Tensor], ctrl: torch.
     return a1
 
 
+def conv12_fwd_draft(images_u8: torch.Tensor, idx: Optional[torch.Tensor], ctrl: torch.Tensor, w1: torch.Tensor,
+                     b1: torch.Tensor, w2: torch.Tensor, b2: torch.Tensor, batch: int):
+    """DRAFT kernel (tc_conv2_v4.cu, never run on a GPU yet): conv1 + conv2 forward in one launch."""
+    a1 = torch.empty(batch, 26, 26, 32, device="cuda")
+    pooled = torch.empty(batch, 12, 12, 64, device="cuda")
+    amax = torch.empty(batch, 12, 12, 64, dtype=torch.uint8, device="cuda")
+    N.check(N.lib().b200_conv12_fwd_tc4(_p(images_u8), _p(idx), _p(ctrl), _p(w1), _p(b1), _p(a1), _p(w2), _p(b2),
+                                        _p(pooled), _p(amax), batch, _s()))
+    return a1, pooled, amax
+
+
 def conv1_wgrad(images_u8, idx, ctrl, da1: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
     batch = da1.shape[0]
     part = torch.empty(2 * batch, 320, device="cuda")

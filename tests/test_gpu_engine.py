@@ -45,7 +45,7 @@ def _tc_masks():
     return [0, 15, 31, 63] if N.lib().b200_has_tc() else [0]
 
 
-@pytest.mark.parametrize("use_tc", [0, 15, 31, 63] + ([127] if __import__("os").environ.get("B200_DRAFT") == "1" else []))  # 127 = + draft dY-free dgrad
+@pytest.mark.parametrize("use_tc", [0, 15, 31, 63] + ([127, 255] if __import__("os").environ.get("B200_DRAFT") == "1" else []))  # 64 / 128 = draft kernels of tc_conv2_v4.cu
 @pytest.mark.parametrize("batch", [64, 200])
 def test_train_step_matches_torch_without_dropout(use_tc, batch):
     if use_tc not in _tc_masks():

@@ -241,6 +241,28 @@ def test_conv2_dgrad_draft_v4_equals_v3(ops, batch):
     assert torch.equal(ref, got), (ref - got).abs().max().item()
 
 
+@pytest.mark.skipif(os.environ.get("B200_DRAFT") != "1",
+                    reason="draft kernel (tc_conv2_v4.cu) has never run on a GPU yet; set B200_DRAFT=1 to try it")
+@pytest.mark.parametrize("train", [False, True])
+@pytest.mark.parametrize("batch", [1, 7, 64, 200])
+def test_conv12_fwd_draft_v4_equals_conv1_then_conv2_v3(ops, batch, train):
+    """The fused conv1+conv2 forward must reproduce conv1_fwd followed by the v3 conv2 forward bit for bit
+    (same FMA order in conv1, same MMAs and epilogue in conv2, same Philox offsets)."""
+    _need_tc(True)
+    net, imgs = _net(), _images(300)
+    w = _internal(net)
+    idx = torch.randperm(300)[: batch + 5].to(torch.int32).cuda()
+    ctrl = ops.make_ctrl(pos=3, step=5, seed=11, train=train)
+    a1_ref = ops.conv1_fwd(imgs, idx, ctrl, w["conv1.weight"], w["conv1.bias"], batch)
+    pooled_ref, amax_ref = ops.conv2_fwd(a1_ref, w["conv2.weight"], w["conv2.bias"], ctrl, tc=3)
+    a1, pooled, amax = ops.conv12_fwd_draft(imgs, idx, ctrl, w["conv1.weight"], w["conv1.bias"], w["conv2.weight"],
+                                            w["conv2.bias"], batch)
+    torch.cuda.synchronize()
+    assert torch.equal(a1, a1_ref), (a1 - a1_ref).abs().max().item()
+    assert torch.equal(pooled, pooled_ref), (pooled - pooled_ref).abs().max().item()
+    assert torch.equal(amax, amax_ref)
+
+
 @pytest.mark.parametrize("batch", [1, 7, 64])
 def test_conv1_wgrad(ops, batch):
     net, imgs = _net(), _images(100)
