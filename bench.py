@@ -59,20 +59,58 @@ class ClockSampler:
             self.thread.start()
         except Exception:
             self.proc = None
+        # A timed region of a few tens of milliseconds is shorter than nvidia-smi's polling period, so the same
+        # quantities are also polled through NVML every 5 ms from a thread (best effort: any failure -> skipped)
+        self.nvml_rows, self._nvml_stop = [], threading.Event()
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            h = pynvml.nvmlDeviceGetHandleByIndex(self.gpu)
+            mx = float(pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM))
+
+            def poll():
+                while not self._nvml_stop.is_set():
+                    try:
+                        sm = float(pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM))
+                        try:
+                            mask = int(pynvml.nvmlDeviceGetCurrentClocksEventReasons(h))
+                        except Exception:
+                            mask = int(pynvml.nvmlDeviceGetCurrentClocksThrottleReasons(h))
+                        try:
+                            power = pynvml.nvmlDeviceGetPowerUsage(h) / 1000.0
+                        except Exception:
+                            power = None
+                        self.nvml_rows.append((sm, mx, power, mask))
+                    except Exception:
+                        return
+                    time.sleep(0.005)
+
+            self.nvml_thread = threading.Thread(target=poll, daemon=True)
+            self.nvml_thread.start()
+        except Exception:
+            self.nvml_thread = None
+
+    def n_samples(self) -> int:
+        return len(self.rows) + len(getattr(self, "nvml_rows", []))
 
     def _pump(self) -> None:
         for line in self.proc.stdout:
             self.rows.append(line.strip())
 
     def stop(self) -> dict:
-        if self.proc is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=2)
-        except Exception:
-            self.proc.kill()
+        if getattr(self, "nvml_thread", None) is not None:
+            self._nvml_stop.set()
+            self.nvml_thread.join(timeout=1)
+        nvml_rows = list(getattr(self, "nvml_rows", []))
+        if self.proc is None and not nvml_rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi and NVML unavailable"]}
+        if self.proc is not None:
+            time.sleep(0.15)
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except Exception:
+                self.proc.kill()
         sm, mx, power, reasons = [], [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         for r in self.rows:
@@ -86,8 +124,18 @@ class ClockSampler:
             for name, val in zip(names, f[5:9]):
                 if val.lower().startswith("active"):
                     reasons.add(name)
+        smi_samples = len(sm)
+        bits = {"hw_slowdown": 0x8, "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20, "sw_power_cap": 0x4}
+        for s_, m_, p_, mask in nvml_rows:
+            sm.append(s_); mx.append(m_)
+            if p_ is not None:
+                power.append(p_)
+            for name, bit in bits.items():
+                if mask & bit:
+                    reasons.add(name)
         return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "power_w_max": max(power) if power else None, "samples": len(sm), "reasons": sorted(reasons)}
+                "power_w_max": max(power) if power else None, "samples": len(sm),
+                "samples_nvidia_smi": smi_samples, "samples_nvml": len(nvml_rows), "reasons": sorted(reasons)}
 
 
 def _dist_env():
@@ -204,7 +252,31 @@ def run_ours(args) -> dict:
     e1.record()
     barrier()
     e2e_ms = e0.elapsed_time(e1)
+    # A very short run can end before the first clock sample arrives: keep the same workload running (untimed)
+    # until there are a few samples, and say so in the record.
+    extended, j_ext = False, W + K
+
+    def too_few_samples() -> bool:
+        # every rank must run the same number of steps (the fused all-reduce kernels wait for their peers),
+        # so the decision is taken on the minimum over ranks
+        n = torch.tensor([sampler.n_samples()], device="cuda", dtype=torch.int32)
+        if world > 1:
+            import torch.distributed as dist
+            dist.all_reduce(n, op=dist.ReduceOp.MIN)
+        return int(n.item()) < 3
+
+    for _ in range(12):  # at most ~12 x 64 steps (~0.15 s of GPU time at batch 200)
+        if not too_few_samples():
+            break
+        extended = True
+        for _ in range(64):
+            e2e_step(j_ext, 0)
+            j_ext += 1
+        torch.cuda.synchronize()
+        time.sleep(0.02)
     clocks = sampler.stop()
+    if extended:
+        clocks["note"] = "timed region shorter than the sampling period: samples include untimed steps of the same workload run right after it"
     host_loss = torch.stack([eng.host_loss_ring[s % LOSS_RING] for s in steps_e2e[-min(K, LOSS_RING):]]).clone()
     losses_ok = bool(torch.isfinite(host_loss).all()) and float(host_loss.abs().sum()) > 0
 
