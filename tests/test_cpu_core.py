@@ -269,3 +269,33 @@ def test_init_distributed_mode_discovery_branches(branch, monkeypatch, capsys):
     assert calls["rank"] == want[0] and calls["world_size"] == want[1]
     # banner format of mnist_ddp.py:34
     assert out.strip() == f"| distributed init (rank {want[0]}): env://, local rank:{want[2]}, world size:{want[1]}"
+
+
+def test_bench_clock_sampler_nvml_path_and_graceful_absence(monkeypatch):
+    """bench.ClockSampler: NVML polling (stubbed) yields clocks + throttle reasons; no driver -> a clear record."""
+    import time
+    import types
+    sys.path.insert(0, ROOT)
+    import bench
+    stub = types.ModuleType("pynvml")
+    stub.NVML_CLOCK_SM = 1
+    stub.nvmlInit = lambda: None
+    stub.nvmlDeviceGetHandleByIndex = lambda i: i
+    stub.nvmlDeviceGetMaxClockInfo = lambda h, t: 1965
+    stub.nvmlDeviceGetClockInfo = lambda h, t: 1950
+    stub.nvmlDeviceGetCurrentClocksEventReasons = lambda h: 0x4 | 0x40
+    stub.nvmlDeviceGetPowerUsage = lambda h: 300000
+    monkeypatch.setitem(sys.modules, "pynvml", stub)
+    monkeypatch.setenv("PATH", "/nonexistent")  # no nvidia-smi
+    c = bench.ClockSampler(0)
+    c.start()
+    time.sleep(0.05)
+    assert c.n_samples() >= 3
+    rec = c.stop()
+    assert rec["sm_mhz"] == 1950.0 and rec["sm_max_mhz"] == 1965.0 and rec["samples_nvml"] >= 3
+    assert rec["reasons"] == ["hw_thermal_slowdown", "sw_power_cap"]
+    stub.nvmlInit = lambda: (_ for _ in ()).throw(RuntimeError("no driver"))
+    c = bench.ClockSampler(0)
+    c.start()
+    rec = c.stop()
+    assert rec["sm_mhz"] is None and "unavailable" in rec["reasons"][0]
