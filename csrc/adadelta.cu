@@ -45,41 +45,43 @@ adadelta_kernel(float* __restrict__ p, const float* __restrict__ g, float* __res
   }
 }
 
-// Single-GPU end-of-step kernel when the conv-bucket gradients are still per-CTA partial sums:
-// CTAs [0, nchunks) each own 256 floats of the conv bucket (reduce partials in a fixed order, then
-// Adadelta); the remaining CTAs stream over the fc bucket.  Replaces four reduction launches plus the
-// plain Adadelta launch.
-__global__ void __launch_bounds__(1024)
+// conv2's half of the conv bucket on one GPU: reduce the wgrad kernel's per-CTA partial rows into the
+// gradient buffer.  Runs on the wgrad branch, under conv2 dgrad / conv1 wgrad (11 MB of partials at 148
+// CTAs would otherwise be read by the step's last kernel).  One CTA per 256-float chunk.
+__global__ void __launch_bounds__(64 * FIN_SLICES)
+reduce_segs_kernel(float* __restrict__ dst, FinalizeSegs segs) {
+  __shared__ float4 red[FIN_SLICES][64];
+  pdl_trigger();
+  pdl_wait();
+  const int off = blockIdx.x * 256;
+  const float4 t = reduce_partial_chunk(segs, off, red);
+  if (threadIdx.x < 64) *reinterpret_cast<float4*>(dst + off + 4 * threadIdx.x) = t;
+}
+
+// Single-GPU end-of-step kernel.  CTAs [0, nchunks) each own 256 floats of the conv bucket: chunks below
+// first_partial already have their gradient in g (conv2, reduced on the wgrad branch), the others (conv1)
+// reduce their partial rows in a fixed order first; then Adadelta.  The remaining CTAs stream over the fc
+// bucket unless that was updated on the fc branch already.  The last CTA to finish advances the step.
+__global__ void __launch_bounds__(64 * FIN_SLICES)
 adadelta_finalize_kernel(float* __restrict__ p, float* __restrict__ g, float* __restrict__ v, float* __restrict__ u,
-                         int b0_n4, int b1_off, int nchunks, FinalizeSegs segs, B200Ctrl* __restrict__ ctrl, float rho,
-                         float eps, int advance, unsigned int* __restrict__ done_counter) {
+                         int b0_n4, int b1_off, int nchunks, int first_partial, FinalizeSegs segs,
+                         B200Ctrl* __restrict__ ctrl, float rho, float eps, int advance,
+                         unsigned int* __restrict__ done_counter) {
   __shared__ float4 red[FIN_SLICES][64];
   pdl_trigger();
   pdl_wait();
   const float lr = ctrl->lr;
   if ((int)blockIdx.x < nchunks) {
-    const int col = threadIdx.x & 63, slice = threadIdx.x >> 6, off = blockIdx.x * 256;
-    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      const FinalizeSegs::Seg sg = segs.seg[k];
-      const int e = off - sg.dst_off + 4 * col;
-      if (sg.src && e >= 0 && e < sg.n) {
-#pragma unroll 8
-        for (int q = slice; q < sg.nparts; q += FIN_SLICES) {
-          const float4 x = *reinterpret_cast<const float4*>(sg.src + (size_t)q * sg.stride + e);
-          acc.x += x.x; acc.y += x.y; acc.z += x.z; acc.w += x.w;
-        }
-      }
+    const int col = threadIdx.x & 63, off = blockIdx.x * 256;
+    const size_t i = (size_t)b1_off + off + 4 * col;
+    float4 t;
+    if ((int)blockIdx.x >= first_partial) {
+      t = reduce_partial_chunk(segs, off, red);
+      if (threadIdx.x < 64) *reinterpret_cast<float4*>(g + i) = t;  // keep the gradient buffer complete (tests, debugging)
+    } else if (threadIdx.x < 64) {
+      t = *reinterpret_cast<const float4*>(g + i);
     }
-    red[slice][col] = acc;
-    __syncthreads();
-    if (slice == 0) {
-      float4 t = red[0][col];
-#pragma unroll
-      for (int q = 1; q < FIN_SLICES; ++q) { const float4 x = red[q][col]; t.x += x.x; t.y += x.y; t.z += x.z; t.w += x.w; }
-      const size_t i = (size_t)b1_off + off + 4 * col;
-      *reinterpret_cast<float4*>(g + i) = t;  // keep the gradient buffer complete (tests, debugging)
+    if (threadIdx.x < 64) {
       float4 pp = *reinterpret_cast<float4*>(p + i), vv = *reinterpret_cast<float4*>(v + i),
              uu = *reinterpret_cast<float4*>(u + i);
       adadelta_update(t.x, pp.x, vv.x, uu.x, lr, rho, eps);
@@ -118,16 +120,25 @@ adadelta_finalize_kernel(float* __restrict__ p, float* __restrict__ g, float* __
   }
 }
 
-// bucket 0 = floats [0, b1_off) (fc), bucket 1 = floats [b1_off, b1_off + 256*nchunks) (conv, as partials)
-int b200_adadelta_finalize(float* p, float* g, float* v, float* u, long b1_off, int nchunks, const FinalizeSegs& segs,
-                           void* ctrl, float rho, float eps, int advance, unsigned int* done_counter,
-                           bool bucket0_done, cudaStream_t s) {
-  B200_REQUIRE(b1_off % 4 == 0 && nchunks > 0, "adadelta_finalize: bad bucket layout");
+int b200_reduce_segs(float* dst, int nchunks, const FinalizeSegs& segs, cudaStream_t s) {
+  B200_REQUIRE(dst && nchunks > 0, "reduce_segs: bad arguments");
+  B200_CHECK(b200_launch(reduce_segs_kernel, dim3(nchunks), dim3(64 * FIN_SLICES), 0, s, dst, segs));
+  b200_count_launch();
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+// bucket 0 = floats [0, b1_off) (fc), bucket 1 = floats [b1_off, b1_off + 256*nchunks) (conv)
+int b200_adadelta_finalize(float* p, float* g, float* v, float* u, long b1_off, int nchunks, int first_partial,
+                           const FinalizeSegs& segs, void* ctrl, float rho, float eps, int advance,
+                           unsigned int* done_counter, bool bucket0_done, cudaStream_t s) {
+  B200_REQUIRE(b1_off % 4 == 0 && nchunks > 0 && first_partial >= 0 && first_partial <= nchunks,
+               "adadelta_finalize: bad bucket layout");
   // bucket0_done: the fc bucket was already updated elsewhere (engine branch stream); only the conv chunks run
   const int grid = nchunks + (bucket0_done ? 0 : 2 * b200_sm_count());
   B200_CHECK(b200_launch(adadelta_finalize_kernel, dim3(grid), dim3(64 * FIN_SLICES), 0, s, p, g, v, u,
-                         bucket0_done ? 0 : (int)(b1_off / 4),
-                         (int)b1_off, nchunks, segs, (B200Ctrl*)ctrl, rho, eps, advance, done_counter));
+                         bucket0_done ? 0 : (int)(b1_off / 4), (int)b1_off, nchunks, first_partial, segs,
+                         (B200Ctrl*)ctrl, rho, eps, advance, done_counter));
   b200_count_launch();
   B200_LAUNCH_CHECK();
   return B200_OK;

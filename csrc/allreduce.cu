@@ -34,9 +34,13 @@ namespace {
 struct CommArgs {
   const float* grad[SYMM_MAX_WORLD];  // start of the bucket in every rank's gradient buffer
   float* param[SYMM_MAX_WORLD];       // start of the bucket in every rank's parameter (or output) buffer
+  float* red[SYMM_MAX_WORLD];         // start of the bucket in every rank's reduced-gradient buffer (or null)
   uint32_t* flags[SYMM_MAX_WORLD];    // every rank's flag block
-  const float* mc_grad;               // NVLS multicast aliases of the same two buffers (or null)
+  const float* mc_grad;               // NVLS multicast aliases of the same three buffers (or null)
   float* mc_param;
+  float* mc_red;
+  CommFault* fault;                   // mapped pinned host record a timed-out barrier fills in before it traps (or null)
+  unsigned long long timeout_ns;      // how long a barrier waits for a peer before giving up
   float* v;                           // local Adadelta state (bucket start); unused when OPT == false
   float* u;
   const B200Ctrl* ctrl;               // lr and step counter; may be null when token != 0 and OPT == false
@@ -74,22 +78,62 @@ __device__ __forceinline__ void st_peer_f4(float* p, float4 v) {
   asm volatile("st.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
 }
 
+__device__ __forceinline__ unsigned long long global_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+// Waits until *p has reached tok.  A peer that never arrives must not hang the GPU: after timeout_ns the
+// waiting thread records who waited for whom in mapped host memory (the host prints it, symm.cu:
+// b200_comm_fault_message) and traps, which ends the process with a launch failure instead of a hang.
+__device__ __noinline__ void comm_wait_timeout(const CommArgs& a, int kind, int peer, uint32_t tok, uint32_t seen) {
+  CommFault* f = a.fault;
+  if (f && atomicCAS(&f->valid, 0u, 1u) == 0u) {
+    f->rank = a.rank; f->world = a.world; f->channel = a.channel; f->kind = kind; f->block = blockIdx.x;
+    f->peer = peer; f->expected = tok; f->seen = seen; f->step = a.ctrl ? a.ctrl->step : 0ull;
+    f->waited_ns = a.timeout_ns;
+    __threadfence_system();
+    f->valid = 2u;
+    __threadfence_system();
+  }
+  __trap();
+}
+__device__ __forceinline__ void comm_wait(const CommArgs& a, const uint32_t* p, uint32_t tok, int kind, int peer) {
+  uint32_t seen = ld_acquire_sys(p);
+  if ((int32_t)(seen - tok) >= 0) return;
+  const unsigned long long t0 = global_ns();
+  uint32_t spins = 0;
+  while ((int32_t)((seen = ld_acquire_sys(p)) - tok) < 0) {
+    if ((++spins & 1023u) == 0 && global_ns() - t0 > a.timeout_ns) comm_wait_timeout(a, kind, peer, tok, seen);
+  }
+}
+
 // phase 0 = "my gradients are complete", phase 1 = "I have finished reading / my writes are out".
-// No explicit fence is needed before the signal: gradients were written by EARLIER kernels (a kernel
-// boundary makes them visible system-wide), and the st.release.sys that follows the CTA barrier is
-// cumulative over everything the CTA's threads wrote before that barrier (two-shot parameter stores).
-__device__ __forceinline__ void comm_barrier(const CommArgs& a, int phase, uint32_t tok) {
+// No explicit fence is needed before the signal: gradients written by EARLIER kernels are visible
+// system-wide at the kernel boundary, and the st.release.sys that follows the CTA barrier is cumulative
+// over everything the CTA's threads wrote before that barrier (gradient chunks reduced in the same kernel,
+// two-shot parameter stores).
+__device__ __forceinline__ void comm_barrier(const CommArgs& a, int channel, int phase, uint32_t tok) {
   __syncthreads();
   if ((int)threadIdx.x < a.world) {
-    const int idx = ((a.channel * 2 + phase) * SYMM_MAX_BLOCKS + blockIdx.x) * SYMM_MAX_WORLD;
+    const int idx = ((channel * 2 + phase) * SYMM_MAX_BLOCKS + blockIdx.x) * SYMM_MAX_WORLD;
     st_release_sys(a.flags[threadIdx.x] + idx + a.rank, tok);
-    const uint32_t* mine = a.flags[a.rank] + idx + threadIdx.x;
-    uint32_t spins = 0;
-    while ((int32_t)(ld_acquire_sys(mine) - tok) < 0) {
-      if (++spins > (1u << 27)) __trap();  // a peer never arrived: fail loudly instead of hanging
-    }
+    comm_wait(a, a.flags[a.rank] + idx + threadIdx.x, tok, phase, threadIdx.x);
   }
   __syncthreads();
+}
+// Gather form for chunk-owner kernels: every rank tells the OWNER of this CTA's chunk that its share is
+// ready; only the owner waits.  (W-1) flag stores per chunk instead of W*(W-1).
+__device__ __forceinline__ void comm_signal_owner(const CommArgs& a, int channel, int owner, uint32_t tok) {
+  __syncthreads();
+  const int idx = ((channel * 2) * SYMM_MAX_BLOCKS + blockIdx.x) * SYMM_MAX_WORLD;
+  if (a.rank != owner) {
+    if (threadIdx.x == 0) st_release_sys(a.flags[owner] + idx + a.rank, tok);
+  } else {
+    if ((int)threadIdx.x < a.world && (int)threadIdx.x != owner)
+      comm_wait(a, a.flags[owner] + idx + threadIdx.x, tok, 2, threadIdx.x);
+    __syncthreads();
+  }
 }
 
 // advance > -1: the last CTA to finish also advances the control block (end-of-step marker)
@@ -109,7 +153,7 @@ fused_allreduce_kernel(const CommArgs* __restrict__ table, uint32_t token, float
 #pragma unroll
   for (int q = 0; q < SYMM_MAX_WORLD; ++q) { gp[q] = a.grad[q < W ? q : 0]; pp[q] = a.param[q < W ? q : 0]; }
 
-  comm_barrier(a, 0, tok);
+  comm_barrier(a, a.channel, 0, tok);
 
   int lo = 0, hi = a.n4;
   if (MODE >= 1) {
@@ -160,7 +204,7 @@ fused_allreduce_kernel(const CommArgs* __restrict__ table, uint32_t token, float
   // alternate, and the ENTRY barrier of the next one (which every rank reaches only after this kernel
   // has completed on it) already proves that all peers are done reading / writing.  Stand-alone use
   // (microbenchmark, tests) keeps it.
-  if (exit_barrier) comm_barrier(a, 1, tok + 1u);
+  if (exit_barrier) comm_barrier(a, a.channel, 1, tok + 1u);
   if (advance >= 0 && threadIdx.x == 0) {
     __threadfence();
     if (atomicAdd(done_counter, 1u) == gridDim.x - 1) {  // every CTA has read ctrl->step / lr by now
@@ -172,57 +216,116 @@ fused_allreduce_kernel(const CommArgs* __restrict__ table, uint32_t token, float
   }
 }
 
-// The conv bucket's last kernel: (1) reduce the per-CTA partial sums that the wgrad kernels left behind
-// into this rank's gradient bucket, (2) one-shot all-reduce across ranks, (3) 1/W + Adadelta, (4) end
-// of step.  One CTA owns 256 consecutive floats of the bucket from start to finish, so the only
-// cross-CTA ordering needed is the per-CTA cross-GPU barrier.  1024 threads = 64 float4 columns x 16
-// partial slices (fixed combination order: deterministic).
-__global__ void __launch_bounds__(1024)
-finalize_bucket_kernel(const CommArgs* __restrict__ table, FinalizeSegs segs, float rho, float eps, int advance,
-                       unsigned int* __restrict__ done_counter, int exit_barrier) {
+// ---- the conv bucket (75 KB): two kernels ------------------------------------------------------------
+// DDP's second bucket is {conv2.weight, conv2.bias, conv1.weight, conv1.bias}; its gradients become ready
+// in two steps, and treating it as ONE all-reduce at the very end (as DDP does, and as round 1 of this
+// code did) leaves the whole cross-GPU latency exposed after the last backward kernel.  Here:
+//
+//  conv2_reduce_kernel (on the conv2-wgrad branch, under conv2 dgrad / conv1 wgrad): one CTA per 256-float
+//    chunk of conv2.{weight,bias}: sum the wgrad kernel's per-CTA partial rows into this rank's gradient
+//    bucket, tell the chunk's owner, and the owner all-reduces the chunk into EVERY rank's reduced-gradient
+//    buffer R (owner = chunk % W; P2P loads in fixed rank order + P2P stores, or multimem.ld_reduce +
+//    multimem.st through the NVSwitch).  One-shot mode: every rank sums the chunk itself into its own R.
+//    The parameters are not touched here: conv2 dgrad is still reading conv2.weight on every rank.
+//  conv_finalize_kernel (last kernel of the step): conv1's chunks (3 of them) are reduced from their
+//    partial rows, exchanged one-shot (every rank reads all W copies in rank order: bit-identical sums and
+//    no second barrier), conv2's chunks are read back from R; then 1/W is already applied, Adadelta runs
+//    on the whole conv bucket, and the last CTA advances the step counter.
+// Ordering without exit barriers: the finalize kernel's entry barrier is passed only when every rank has
+// finished its conv2_reduce (and fc-bucket) kernel, so R and the two-shot parameter stores have landed;
+// a rank reaches the NEXT step's communication kernels only after its own finalize kernel, so nobody
+// overwrites a gradient chunk or R while a peer may still read the previous step's value.
+template <int MODE>
+__global__ void __launch_bounds__(64 * FIN_SLICES)
+conv2_reduce_kernel(const CommArgs* __restrict__ table, FinalizeSegs segs, const FinalizeSegs* __restrict__ segs_emul,
+                    int channel) {
   __shared__ float4 red[FIN_SLICES][64];
   pdl_trigger();
   pdl_wait();
-  const CommArgs& a = table[0];
+  const CommArgs& a = table[blockIdx.y];
+  if (segs_emul) segs = segs_emul[blockIdx.y];
+  const int W = a.world, r = a.rank;
+  const uint32_t tok = (uint32_t)(a.ctrl->step) * 2u + 1u;
+  const int col = threadIdx.x & 63, off = blockIdx.x * 256;
+  const size_t i4 = (size_t)off + 4 * col;
+  const float4 t = reduce_partial_chunk(segs, off, red);
+  if (threadIdx.x < 64) *reinterpret_cast<float4*>(const_cast<float*>(a.grad[r]) + i4) = t;
+  if (MODE == 0) {
+    comm_barrier(a, channel, 0, tok);
+    if (threadIdx.x < 64) {
+      float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int q = 0; q < SYMM_MAX_WORLD; ++q) {
+        if (q < W) {  // fixed rank order on every rank: bit-identical sums
+          const float4 g = ld_peer_f4(a.grad[q] + i4);
+          s.x += g.x; s.y += g.y; s.z += g.z; s.w += g.w;
+        }
+      }
+      s.x *= a.inv_world; s.y *= a.inv_world; s.z *= a.inv_world; s.w *= a.inv_world;
+      *reinterpret_cast<float4*>(a.red[r] + i4) = s;
+    }
+  } else {
+    const int owner = blockIdx.x % W;
+    comm_signal_owner(a, channel, owner, tok);
+    if (r == owner && threadIdx.x < 64) {
+      float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (MODE == 2) {
+        s = multimem_ld_reduce_f4(a.mc_grad + i4);  // in-switch reduction (NVLS)
+      } else {
+#pragma unroll
+        for (int q = 0; q < SYMM_MAX_WORLD; ++q) {
+          if (q < W) {
+            const float4 g = ld_peer_f4(a.grad[q] + i4);
+            s.x += g.x; s.y += g.y; s.z += g.z; s.w += g.w;
+          }
+        }
+      }
+      s.x *= a.inv_world; s.y *= a.inv_world; s.z *= a.inv_world; s.w *= a.inv_world;
+      if (MODE == 2) {
+        multimem_st_f4(a.mc_red + i4, s);  // one store, delivered to every rank
+        __threadfence_system();
+      } else {
+#pragma unroll
+        for (int q = 0; q < SYMM_MAX_WORLD; ++q)
+          if (q < W) st_peer_f4(a.red[q] + i4, s);
+      }
+    }
+  }
+}
+
+__global__ void __launch_bounds__(64 * FIN_SLICES)
+conv_finalize_kernel(const CommArgs* __restrict__ table, FinalizeSegs segs, const FinalizeSegs* __restrict__ segs_emul,
+                     int first_partial, float rho, float eps, int advance, unsigned int* __restrict__ done_counter) {
+  __shared__ float4 red[FIN_SLICES][64];
+  pdl_trigger();
+  pdl_wait();
+  const CommArgs& a = table[blockIdx.y];
+  if (segs_emul) segs = segs_emul[blockIdx.y];
   const int W = a.world, r = a.rank;
   const uint32_t tok = (uint32_t)(a.ctrl->step) * 2u + 1u;
   const float lr = a.ctrl->lr;
-  const int col = threadIdx.x & 63, slice = threadIdx.x >> 6;
-  const int off = blockIdx.x * 256;
-  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-  for (int k = 0; k < 4; ++k) {
-    const FinalizeSegs::Seg sg = segs.seg[k];
-    const int e = off - sg.dst_off + 4 * col;
-    if (sg.src && e >= 0 && e < sg.n) {
-#pragma unroll 8
-      for (int p = slice; p < sg.nparts; p += FIN_SLICES) {
-        const float4 v = *reinterpret_cast<const float4*>(sg.src + (size_t)p * sg.stride + e);
-        acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
-      }
-    }
+  const int col = threadIdx.x & 63, off = blockIdx.x * 256;
+  const size_t i4 = (size_t)off + 4 * col;
+  const bool partial = (int)blockIdx.x >= first_partial;  // conv1: still partial rows; conv2: already in R
+  if (partial) {
+    const float4 t = reduce_partial_chunk(segs, off, red);
+    if (threadIdx.x < 64) *reinterpret_cast<float4*>(const_cast<float*>(a.grad[r]) + i4) = t;
   }
-  red[slice][col] = acc;
-  __syncthreads();
-  float* mygrad = const_cast<float*>(a.grad[r]) + off + 4 * col;
-  if (slice == 0) {
-    float4 t = red[0][col];
-#pragma unroll
-    for (int q = 1; q < FIN_SLICES; ++q) { const float4 v = red[q][col]; t.x += v.x; t.y += v.y; t.z += v.z; t.w += v.w; }
-    *reinterpret_cast<float4*>(mygrad) = t;
-  }
-  comm_barrier(a, 0, tok);  // release is cumulative over the gradient stores above
-  if (slice == 0) {
-    const size_t i4 = (size_t)off + 4 * col;
+  comm_barrier(a, a.channel, 0, tok);  // release is cumulative over the gradient stores above
+  if (threadIdx.x < 64) {
     float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (partial) {
 #pragma unroll
-    for (int q = 0; q < SYMM_MAX_WORLD; ++q) {
-      if (q < W) {
-        const float4 g = ld_peer_f4(a.grad[q] + i4);
-        s.x += g.x; s.y += g.y; s.z += g.z; s.w += g.w;
+      for (int q = 0; q < SYMM_MAX_WORLD; ++q) {
+        if (q < W) {
+          const float4 g = ld_peer_f4(a.grad[q] + i4);
+          s.x += g.x; s.y += g.y; s.z += g.z; s.w += g.w;
+        }
       }
+      s.x *= a.inv_world; s.y *= a.inv_world; s.z *= a.inv_world; s.w *= a.inv_world;
+    } else {
+      s = ld_peer_f4(a.red[r] + i4);  // written by the chunk's owner during conv2_reduce_kernel
     }
-    s.x *= a.inv_world; s.y *= a.inv_world; s.z *= a.inv_world; s.w *= a.inv_world;
     float4 p = *reinterpret_cast<const float4*>(a.param[r] + i4);
     float4 vv = *reinterpret_cast<const float4*>(a.v + i4);
     float4 uu = *reinterpret_cast<const float4*>(a.u + i4);
@@ -234,14 +337,16 @@ finalize_bucket_kernel(const CommArgs* __restrict__ table, FinalizeSegs segs, fl
     *reinterpret_cast<float4*>(a.u + i4) = uu;
     *reinterpret_cast<float4*>(a.param[r] + i4) = p;
   }
-  if (exit_barrier) comm_barrier(a, 1, tok + 1u);  // see fused_allreduce_kernel
-  if (advance >= 0 && threadIdx.x == 0) {
-    __threadfence();
-    if (atomicAdd(done_counter, 1u) == gridDim.x - 1) {
-      *done_counter = 0;
-      B200Ctrl* c = const_cast<B200Ctrl*>(a.ctrl);
-      c->step += 1;
-      c->pos += advance;
+  if (advance >= 0) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      __threadfence();
+      if (atomicAdd(done_counter + blockIdx.y, 1u) == gridDim.x - 1) {  // every CTA has read ctrl->step / lr by now
+        done_counter[blockIdx.y] = 0;
+        B200Ctrl* c = const_cast<B200Ctrl*>(a.ctrl);
+        c->step += 1;
+        c->pos += advance;
+      }
     }
   }
 }
@@ -250,28 +355,46 @@ struct CommPlan {
   CommArgs* dev = nullptr;  // world_slots entries (1, or W when emulated)
   int slots = 1;
   int n4 = 0, world = 1;
-  bool has_mc = false;
+  bool has_mc = false, has_red = false;
 };
 
+unsigned long long comm_timeout_ns() {
+  // how long a barrier waits for a peer (B200_COMM_TIMEOUT_MS, default 60 s): long enough for rank-0-only work
+  // between steps (evaluation, checkpoint writing, a blocked stdout pipe), short enough to end a dead job
+  static const unsigned long long ns = [] {
+    const char* e = getenv("B200_COMM_TIMEOUT_MS");
+    const double ms = e ? atof(e) : 60000.0;
+    return (unsigned long long)((ms > 0 ? ms : 60000.0) * 1e6);
+  }();
+  return ns;
+}
+
+// r_off: float offset of the reduced-gradient region inside the arena payload, or (size_t)-1 for none
 int plan_from_arenas(SymmArena* const* arenas, int slots, size_t grad_off, size_t param_off, size_t v_off,
-                     size_t u_off, size_t n_floats, int channel, const B200Ctrl* const* ctrls, CommPlan** out) {
+                     size_t u_off, size_t r_off, size_t n_floats, int channel, const B200Ctrl* const* ctrls,
+                     CommPlan** out) {
   B200_REQUIRE(n_floats % 4 == 0 && grad_off % 4 == 0 && param_off % 4 == 0, "comm plan: offsets/size must be x4 floats");
   B200_REQUIRE(channel >= 0 && channel < SYMM_CHANNELS, "comm plan: channel %d out of range", channel);
+  const bool has_red = r_off != (size_t)-1;
   std::vector<CommArgs> host(slots);
   for (int sidx = 0; sidx < slots; ++sidx) {
     SymmArena* a = arenas[sidx];
-    B200_REQUIRE((grad_off + n_floats) * 4 <= a->payload && (param_off + n_floats) * 4 <= a->payload,
-                 "comm plan: bucket exceeds the arena payload");
+    B200_REQUIRE((grad_off + n_floats) * 4 <= a->payload && (param_off + n_floats) * 4 <= a->payload &&
+                 (!has_red || (r_off + n_floats) * 4 <= a->payload), "comm plan: bucket exceeds the arena payload");
     CommArgs& c = host[sidx];
     memset(&c, 0, sizeof(c));
     for (int q = 0; q < a->world; ++q) {
       B200_REQUIRE(a->peer[q], "comm plan: rank %d is not mapped (import the IPC handles first)", q);
       c.grad[q] = (const float*)a->peer[q] + grad_off;
       c.param[q] = (float*)a->peer[q] + param_off;
+      c.red[q] = has_red ? (float*)a->peer[q] + r_off : nullptr;
       c.flags[q] = a->flags(q);
     }
     c.mc_grad = a->mc ? (const float*)a->mc + grad_off : nullptr;
     c.mc_param = a->mc ? (float*)a->mc + param_off : nullptr;
+    c.mc_red = (a->mc && has_red) ? (float*)a->mc + r_off : nullptr;
+    c.fault = symm_fault_record(a);
+    c.timeout_ns = comm_timeout_ns();
     c.v = (float*)a->peer[a->rank] + v_off;
     c.u = (float*)a->peer[a->rank] + u_off;
     c.ctrl = ctrls ? ctrls[sidx] : nullptr;
@@ -286,6 +409,7 @@ int plan_from_arenas(SymmArena* const* arenas, int slots, size_t grad_off, size_
   p->n4 = (int)(n_floats / 4);
   p->world = arenas[0]->world;
   p->has_mc = arenas[0]->mc != nullptr;
+  p->has_red = has_red;
   B200_CHECK(cudaMalloc(&p->dev, sizeof(CommArgs) * slots));
   B200_CHECK(cudaMemcpy(p->dev, host.data(), sizeof(CommArgs) * slots, cudaMemcpyHostToDevice));
   *out = p;
@@ -301,13 +425,15 @@ int default_blocks(const CommPlan* p, int mode) {
 }
 
 int run_plan(const CommPlan* p, int mode, int opt, uint32_t token, int nblocks, float rho, float eps, cudaStream_t s,
-             int advance = -1, unsigned int* done_counter = nullptr, int exit_barrier = 1, int threads = 512) {
+             int exit_barrier = 1, int threads = 512) {
   B200_REQUIRE(p && mode >= 0 && mode <= 2, "comm run: bad plan/mode");
   B200_REQUIRE(mode != 2 || p->has_mc, "comm run: NVLS mode needs an arena with a multicast mapping");
   if (nblocks <= 0) nblocks = default_blocks(p, mode);
   B200_REQUIRE(nblocks <= SYMM_MAX_BLOCKS, "comm run: at most %d CTAs", SYMM_MAX_BLOCKS);
   dim3 grid(nblocks, p->slots);
   const CommArgs* tab = p->dev;
+  int advance = -1;
+  unsigned int* done_counter = nullptr;
   void* args[] = {(void*)&tab, (void*)&token, (void*)&rho, (void*)&eps, (void*)&advance, (void*)&done_counter,
                   (void*)&exit_barrier};
   const void* fn = mode == 0 ? (opt ? (const void*)fused_allreduce_kernel<0, true> : (const void*)fused_allreduce_kernel<0, false>)
@@ -324,52 +450,77 @@ int run_plan(const CommPlan* p, int mode, int opt, uint32_t token, int nblocks, 
   return B200_OK;
 }
 
+// conv bucket, both kernels.  which: 0 = conv2_reduce (chunks [0, c2_chunks)), 1 = conv_finalize (all chunks).
+// Emulated plans (slots > 1) launch cooperatively with 256-thread CTAs so that W x chunks CTAs are co-resident.
+int run_conv_bucket(const CommPlan* p, int which, int mode, const FinalizeSegs& segs, const FinalizeSegs* segs_emul,
+                    int c2_chunks, int chunks, int channel_c2, int advance, unsigned int* done_counter, cudaStream_t s) {
+  B200_REQUIRE(p && p->has_red, "conv bucket: the plan has no reduced-gradient region");
+  B200_REQUIRE(mode >= 0 && mode <= 2 && (mode != 2 || p->has_mc), "conv bucket: bad mode %d", mode);
+  B200_REQUIRE(chunks * 64 == p->n4 && c2_chunks > 0 && c2_chunks < chunks && chunks <= SYMM_MAX_BLOCKS,
+               "conv bucket: %d chunks (%d of conv2) do not match a plan of %d float4", chunks, c2_chunks, p->n4);
+  B200_REQUIRE(channel_c2 >= 0 && channel_c2 < SYMM_CHANNELS, "conv bucket: bad channel");
+  const CommArgs* tab = p->dev;
+  const int threads = p->slots > 1 ? 256 : 64 * FIN_SLICES;
+  FinalizeSegs sg = segs;
+  float rho = 0.9f, eps = 1e-6f;
+  int first_partial = c2_chunks;
+  if (which == 0) {
+    dim3 grid(c2_chunks, p->slots);
+    if (p->slots == 1) {
+      if (mode == 0) B200_CHECK(b200_launch(conv2_reduce_kernel<0>, grid, dim3(threads), 0, s, tab, sg, segs_emul, channel_c2));
+      else if (mode == 1) B200_CHECK(b200_launch(conv2_reduce_kernel<1>, grid, dim3(threads), 0, s, tab, sg, segs_emul, channel_c2));
+      else B200_CHECK(b200_launch(conv2_reduce_kernel<2>, grid, dim3(threads), 0, s, tab, sg, segs_emul, channel_c2));
+    } else {
+      void* args[] = {(void*)&tab, (void*)&sg, (void*)&segs_emul, (void*)&channel_c2};
+      const void* fn = mode == 0 ? (const void*)conv2_reduce_kernel<0>
+                     : mode == 1 ? (const void*)conv2_reduce_kernel<1> : (const void*)conv2_reduce_kernel<2>;
+      B200_CHECK(cudaLaunchCooperativeKernel(fn, grid, dim3(threads), args, 0, s));
+    }
+  } else {
+    dim3 grid(chunks, p->slots);
+    if (p->slots == 1) {
+      B200_CHECK(b200_launch(conv_finalize_kernel, grid, dim3(threads), 0, s, tab, sg, segs_emul, first_partial, rho, eps,
+                             advance, done_counter));
+    } else {
+      void* args[] = {(void*)&tab, (void*)&sg, (void*)&segs_emul, (void*)&first_partial, (void*)&rho, (void*)&eps,
+                      (void*)&advance, (void*)&done_counter};
+      B200_CHECK(cudaLaunchCooperativeKernel((const void*)conv_finalize_kernel, grid, dim3(threads), args, 0, s));
+    }
+  }
+  b200_count_launch();
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
 // ---- engine hooks ---------------------------------------------------------------------------------
+constexpr int CH_FC = 0, CH_CONV = 1, CH_CONV2 = 3;  // barrier channels (2 = stand-alone calls: tests, microbenchmark)
 struct DdpState {
   CommPlan* plan[2] = {nullptr, nullptr};
   int mode[2] = {0, 0};
-  cudaStream_t comm = nullptr;
-  cudaEvent_t fork = nullptr, join = nullptr;
 };
 
 int hook_bucket_ready(Engine* E, int bucket, cudaStream_t s) {
   DdpState* d = (DdpState*)E->hooks.state;
-  static const bool no_side = getenv("B200_DDP_NO_SIDE") != nullptr;  // diagnostics: serialise bucket 0
-  static const int exit_b = getenv("B200_DDP_EXIT_BARRIER") ? atoi(getenv("B200_DDP_EXIT_BARRIER")) : 0;
-  if (bucket == 0 && no_side) return run_plan(d->plan[0], d->mode[0], 1, 0, 0, 0.9f, 1e-6f, s, -1, nullptr, exit_b);
   if (bucket == 0) {
-    // fc buckets are complete while the conv backward still runs: reduce them on a side stream
-    B200_CHECK(cudaEventRecord(d->fork, s));
-    B200_CHECK(cudaStreamWaitEvent(d->comm, d->fork, 0));
-    // Footprint of the side-stream reducer (env-tunable).  Measured at W = 2 (us/step): 64x512 160.8,
-    // 37x512 167, 148x512 174, 74x256 172, 148x256 186, 148x128 206 — few fat CTAs beat one light CTA per SM.
+    // The fc bucket is complete while the conv backward still runs; `s` is the engine's fc branch.  No exit
+    // barrier: the finalize kernel's entry barrier orders this kernel's peer accesses (see above).
+    // Footprint of the reducer (env-tunable).  Measured at W = 2 (us/step): 64x512 160.8, 37x512 167,
+    // 148x512 174, 74x256 172, 148x256 186, 148x128 206 -- few fat CTAs beat one light CTA per SM.
     static const int nb0 = getenv("B200_DDP_B0_BLOCKS") ? atoi(getenv("B200_DDP_B0_BLOCKS")) : 96;
     static const int th0 = getenv("B200_DDP_B0_THREADS") ? atoi(getenv("B200_DDP_B0_THREADS")) : 512;
-    int r = run_plan(d->plan[0], d->mode[0], 1, 0, min(nb0, SYMM_MAX_BLOCKS), 0.9f, 1e-6f, d->comm, -1, nullptr, exit_b, th0);
-    if (r != B200_OK) return r;
-    B200_CHECK(cudaEventRecord(d->join, d->comm));
-    return B200_OK;
+    static const int exit_b = getenv("B200_DDP_EXIT_BARRIER") ? atoi(getenv("B200_DDP_EXIT_BARRIER")) : 0;
+    return run_plan(d->plan[0], d->mode[0], 1, 0, min(nb0, SYMM_MAX_BLOCKS), 0.9f, 1e-6f, s, exit_b, th0);
   }
-  return B200_OK;  // bucket 1 is launched by hook_step_end (it also advances the control block)
+  if (bucket == 2)  // conv2's partial rows are complete; `s` is the engine's conv2-wgrad branch
+    return run_conv_bucket(d->plan[1], 0, d->mode[1], E->fin_c2, nullptr, E->c2_chunks, E->conv_chunks, CH_CONV2, -1,
+                           nullptr, s);
+  return B200_OK;
 }
 
 int hook_step_end(Engine* E, int advance, cudaStream_t s) {
   DdpState* d = (DdpState*)E->hooks.state;
-  static const bool no_side = getenv("B200_DDP_NO_SIDE") != nullptr;
-  // The conv bucket's kernel is the last one of the step: it waits for the side stream (bucket 0
-  // reads ctrl->step and lr, which this kernel's last CTA advances) and then ends the step.
-  if (!no_side) B200_CHECK(cudaStreamWaitEvent(s, d->join, 0));
-  if (E->fin_valid) {
-    const int chunks = d->plan[1]->n4 / 64;  // the flat layout pads every segment to 256 floats
-    B200_REQUIRE(d->plan[1]->n4 % 64 == 0 && chunks <= SYMM_MAX_BLOCKS, "finalize: bucket 1 has %d float4", d->plan[1]->n4);
-    static const int exit_b = getenv("B200_DDP_EXIT_BARRIER") ? atoi(getenv("B200_DDP_EXIT_BARRIER")) : 0;
-    B200_CHECK(b200_launch(finalize_bucket_kernel, dim3(chunks), dim3(64 * FIN_SLICES), 0, s, (const CommArgs*)d->plan[1]->dev, E->fin,
-                           0.9f, 1e-6f, advance, E->done_counter, exit_b));
-    b200_count_launch();
-    B200_LAUNCH_CHECK();
-    return B200_OK;
-  }
-  return run_plan(d->plan[1], d->mode[1], 1, 0, 0, 0.9f, 1e-6f, s, advance, E->done_counter);
+  return run_conv_bucket(d->plan[1], 1, d->mode[1], E->fin_c1, nullptr, E->c2_chunks, E->conv_chunks, CH_CONV2, advance,
+                         E->done_counter, s);
 }
 
 void hook_destroy(Engine* E) {
@@ -377,9 +528,6 @@ void hook_destroy(Engine* E) {
   if (!d) return;
   for (int k = 0; k < 2; ++k)
     if (d->plan[k]) { cudaFree(d->plan[k]->dev); delete d->plan[k]; }
-  if (d->comm) cudaStreamDestroy(d->comm);
-  if (d->fork) cudaEventDestroy(d->fork);
-  if (d->join) cudaEventDestroy(d->join);
   delete d;
   E->hooks.state = nullptr;
 }
@@ -394,23 +542,64 @@ extern "C" int b200_comm_plan_create(void* arena, size_t grad_off, size_t param_
   SymmArena* a = (SymmArena*)arena;
   const B200Ctrl* c = (const B200Ctrl*)ctrl;
   CommPlan* p = nullptr;
-  int r = plan_from_arenas(&a, 1, grad_off, param_off, v_off, u_off, n_floats, channel, ctrl ? &c : nullptr, &p);
+  int r = plan_from_arenas(&a, 1, grad_off, param_off, v_off, u_off, (size_t)-1, n_floats, channel, ctrl ? &c : nullptr, &p);
   if (r != B200_OK) return r;
   *plan_out = p;
   return B200_OK;
 }
 
-// all `world` emulated arenas at once; ctrls: world control blocks (or NULL)
+// all `world` emulated arenas at once; ctrls: world control blocks (or NULL); r_off: reduced-gradient region or -1
 extern "C" int b200_comm_plan_create_emulated(void** arenas, int world, size_t grad_off, size_t param_off, size_t v_off,
                                               size_t u_off, size_t n_floats, int channel, const void** ctrls,
                                               void** plan_out) {
   B200_REQUIRE(arenas && plan_out && world >= 1 && world <= SYMM_MAX_WORLD, "comm_plan_create_emulated: bad arguments");
   CommPlan* p = nullptr;
-  int r = plan_from_arenas((SymmArena* const*)arenas, world, grad_off, param_off, v_off, u_off, n_floats, channel,
-                           (const B200Ctrl* const*)ctrls, &p);
+  int r = plan_from_arenas((SymmArena* const*)arenas, world, grad_off, param_off, v_off, u_off, (size_t)-1, n_floats,
+                           channel, (const B200Ctrl* const*)ctrls, &p);
   if (r != B200_OK) return r;
   *plan_out = p;
   return B200_OK;
+}
+
+// Emulated conv-bucket plan for single-GPU tests of conv2_reduce_kernel / conv_finalize_kernel: payload layout of
+// every arena in floats [params n][grads n][sq_avg n][acc_delta n][reduced n], n = 256 * chunks.
+extern "C" int b200_comm_conv_plan_create_emulated(void** arenas, int world, size_t n_floats, const void** ctrls,
+                                                   void** plan_out) {
+  B200_REQUIRE(arenas && plan_out && ctrls && world >= 1 && world <= SYMM_MAX_WORLD, "comm_conv_plan_create_emulated: bad arguments");
+  CommPlan* p = nullptr;
+  int r = plan_from_arenas((SymmArena* const*)arenas, world, n_floats, 0, 2 * n_floats, 3 * n_floats, 4 * n_floats, n_floats,
+                           CH_CONV, (const B200Ctrl* const*)ctrls, &p);
+  if (r != B200_OK) return r;
+  *plan_out = p;
+  return B200_OK;
+}
+
+// One emulated conv-bucket exchange: conv2_reduce (mode 0 one-shot / 1 two-shot) then conv_finalize.
+//   c2_parts[r]: rank r's conv2 partial rows [np2][18496]; c1_parts[r]: its conv1 group rows [ng][320];
+//   counters: >= world zero-initialised words.  The conv bucket layout is the engine's:
+//   [conv2.weight 18432 | conv2.bias 256 | conv1.weight 512 | conv1.bias 256].
+extern "C" int b200_comm_conv_bucket_emulated(void* plan, int mode, const float* const* c2_parts, int np2,
+                                              const float* const* c1_parts, int ng, int advance, unsigned int* counters,
+                                              void* stream) {
+  CommPlan* p = (CommPlan*)plan;
+  B200_REQUIRE(p && c2_parts && c1_parts && counters && p->slots >= 1, "comm_conv_bucket_emulated: bad arguments");
+  cudaStream_t s = (cudaStream_t)stream;
+  std::vector<FinalizeSegs> h2(p->slots), h1(p->slots);
+  for (int r = 0; r < p->slots; ++r) {
+    h2[r].seg[0] = {c2_parts[r], np2, 18496, 18432, 0};
+    h2[r].seg[1] = {c2_parts[r] + 18432, np2, 18496, 64, 18432};
+    h1[r].seg[0] = {c1_parts[r], ng, 320, 288, 18688};
+    h1[r].seg[1] = {c1_parts[r] + 288, ng, 320, 32, 19200};
+  }
+  FinalizeSegs* dev = nullptr;
+  B200_CHECK(cudaMalloc(&dev, sizeof(FinalizeSegs) * 2 * p->slots));
+  B200_CHECK(cudaMemcpyAsync(dev, h2.data(), sizeof(FinalizeSegs) * p->slots, cudaMemcpyHostToDevice, s));
+  B200_CHECK(cudaMemcpyAsync(dev + p->slots, h1.data(), sizeof(FinalizeSegs) * p->slots, cudaMemcpyHostToDevice, s));
+  int r = run_conv_bucket(p, 0, mode, h2[0], dev, 73, 76, CH_CONV2, -1, nullptr, s);
+  if (r == B200_OK) r = run_conv_bucket(p, 1, mode, h1[0], dev + p->slots, 73, 76, CH_CONV2, advance, counters, s);
+  cudaStreamSynchronize(s);
+  cudaFree(dev);
+  return r;
 }
 
 extern "C" int b200_comm_plan_destroy(void* plan) {
@@ -421,7 +610,7 @@ extern "C" int b200_comm_plan_destroy(void* plan) {
   return B200_OK;
 }
 
-// mode 0 one-shot, 1 two-shot.  opt 1: fused 1/W + Adadelta (needs ctrl in the plan), 0: plain averaged
+// mode 0 one-shot, 1 two-shot, 2 NVLS.  opt 1: fused 1/W + Adadelta (needs ctrl in the plan), 0: plain averaged
 // all-reduce into the `param_off` buffer.  token 0: derive the barrier token from ctrl->step; otherwise
 // the caller supplies a token that grows by 2 from call to call.  nblocks 0: pick automatically.
 extern "C" int b200_comm_run(void* plan, int mode, int opt, unsigned int token, int nblocks, void* stream) {
@@ -429,27 +618,27 @@ extern "C" int b200_comm_run(void* plan, int mode, int opt, unsigned int token, 
 }
 
 // Installs the data-parallel hooks on an engine whose params/grads/state live in `arena`
-// (payload layout in floats: [params T][grads T][sq_avg T][acc_delta T]).
+// (payload layout in floats: [params T][grads T][sq_avg T][acc_delta T][reduced conv gradients T]).
 extern "C" int b200_ddp_attach(void* engine, void* arena, int mode_bucket0, int mode_bucket1) {
   Engine* E = (Engine*)engine;
   SymmArena* a = (SymmArena*)arena;
   B200_REQUIRE(E && a, "ddp_attach: null argument");
   const size_t T = (size_t)E->cfg.param_floats;
-  B200_REQUIRE(a->payload >= 4 * T * 4, "ddp_attach: arena too small for params+grads+state");
+  B200_REQUIRE(a->payload >= 5 * T * 4, "ddp_attach: arena too small for params+grads+state+reduced gradients");
   B200_REQUIRE((float*)a->peer[a->rank] == E->P && E->G[0] == E->P + T && E->V == E->P + 2 * T && E->U == E->P + 3 * T,
                "ddp_attach: the engine must have been created on this arena's buffers");
+  B200_REQUIRE(mode_bucket0 >= 0 && mode_bucket0 <= 2 && mode_bucket1 >= 0 && mode_bucket1 <= 2, "ddp_attach: bad mode");
+  B200_REQUIRE((mode_bucket0 != 2 && mode_bucket1 != 2) || a->mc, "ddp_attach: NVLS mode needs a multicast mapping");
   DdpState* d = new DdpState();
   d->mode[0] = mode_bucket0;
   d->mode[1] = mode_bucket1;
   const B200Ctrl* ctrl = E->ctrl;
   for (int k = 0; k < 2; ++k) {
     const size_t beg = (size_t)E->cfg.bucket_begin[k], n = (size_t)(E->cfg.bucket_end[k] - E->cfg.bucket_begin[k]);
-    int r = plan_from_arenas(&a, 1, T + beg, beg, 2 * T + beg, 3 * T + beg, n, k, &ctrl, &d->plan[k]);
+    int r = plan_from_arenas(&a, 1, T + beg, beg, 2 * T + beg, 3 * T + beg, k == 1 ? 4 * T + beg : (size_t)-1, n,
+                             k == 0 ? CH_FC : CH_CONV, &ctrl, &d->plan[k]);
     if (r != B200_OK) return r;
   }
-  B200_CHECK(cudaStreamCreateWithFlags(&d->comm, cudaStreamNonBlocking));
-  B200_CHECK(cudaEventCreateWithFlags(&d->fork, cudaEventDisableTiming));
-  B200_CHECK(cudaEventCreateWithFlags(&d->join, cudaEventDisableTiming));
   E->hooks.state = d;
   E->hooks.bucket_ready = hook_bucket_ready;
   E->hooks.step_end = hook_step_end;

@@ -27,6 +27,18 @@
 
 void b200_set_error(const char* fmt, ...);
 void b200_count_launch(int n = 1);
+
+// What a cross-GPU barrier writes into mapped pinned HOST memory when it gives up waiting for a peer (allreduce.cu),
+// just before it traps.  The trap surfaces on the host as "unspecified launch failure"; b200_set_error() looks at the
+// registered records and appends which rank waited for which peer, so the message names the culprit.
+struct CommFault {
+  unsigned int valid;  // 0 empty, 1 being written, 2 complete
+  int rank, world, channel, kind /* 0 entry barrier, 1 exit barrier, 2 chunk owner waiting for contributions */, block, peer;
+  unsigned int expected, seen;
+  unsigned long long step, waited_ns;
+};
+void b200_register_fault_record(CommFault* host_ptr);
+void b200_unregister_fault_record(CommFault* host_ptr);
 // dst[e] = sum_p src[p*stride + e], fixed order (conv1.cu)
 void b200_launch_reduce_partials(float* dst, const float* src, int n, int nparts, int stride, cudaStream_t s);
 int b200_sm_count();
@@ -79,7 +91,7 @@ inline cudaError_t b200_launch_serial(void (*kernel)(KArgs...), dim3 grid, dim3 
 }
 
 // ---- second-level reduction of per-CTA partial rows, inside the producing kernel ---------------------
-// Kernels that leave one partial row per CTA (conv1 wgrad: 2*batch rows, un-pool: ~300 rows) call this
+// Kernels that leave one partial row per CTA (conv1 wgrad: 2*batch rows) call this
 // at their end: of every GROUP_ROWS consecutive CTAs the one that finishes last adds the group's rows
 // (fixed order, so still deterministic) into gpart[group].  The step's final kernel then has ~8x fewer
 // rows to walk through, which is what its latency is made of.  counters: one zero-initialised word per
@@ -113,11 +125,9 @@ __device__ __forceinline__ void group_reduce_rows(const float* part, int stride,
   }
 }
 #endif
-// engine-internal variants of b200_conv1_wgrad / b200_unpool_dense that also combine groups of partial rows
+// engine-internal variant of b200_conv1_wgrad that also combines groups of partial rows
 int b200_conv1_wgrad_grouped(const uint8_t* images, const int32_t* idx, const void* ctrl, const float* da1, float* part,
                              float* gpart, unsigned int* counters, int batch, cudaStream_t s);
-int b200_unpool_dense_grouped(const float* dp, const uint8_t* amax, float* dy, float* db_part, float* db_gpart,
-                              unsigned int* counters, int batch, cudaStream_t s);
 inline int b200_group_count(int rows) { return (rows + 7) / 8; }
 
 // ---- model constants (mnist_ddp.py:42-47) -------------------------------------------------

@@ -218,6 +218,8 @@ extern "C" int b200_reduce_partials(float* dst, const float* src, int n, int npa
 //    address; the real address is looked up with cudaGetSymbolAddress the first time the entry
 //    point runs on a given device (with that device current) and remembered per device.  That
 //    first call per device does the look-up, so make it before starting any stream capture.
+//    The look-up is for the CURRENT device: `stream` must belong to it (a stream of another device
+//    fails with an invalid-resource-handle launch error).
 //  * All calls on one device share the one array, and it keeps whatever the previous call left
 //    in it.  Nothing in it has to start at zero: a call overwrites every partial row it later
 //    reads (rows 0 .. 2*batch-1) before the reduction kernels read them.  Two calls whose kernels
@@ -250,6 +252,9 @@ extern "C" int b200_conv1_wgrad_noalloc_max_batch(void) { return B200_NOALLOC_MA
 extern "C" int b200_conv1_wgrad_noalloc(const uint8_t* images, const int32_t* idx, const void* ctrl, const float* da1,
                                         float* dw, float* db, int batch, void* stream) {
   B200_REQUIRE(batch > 0, "conv1_wgrad_noalloc: batch must be > 0");
+  // idx may be NULL (sequential addressing); everything else is dereferenced on the device
+  B200_REQUIRE(images && ctrl && da1 && dw && db,
+               "conv1_wgrad_noalloc: images, ctrl, da1, dw and db must all be non-NULL device pointers");
   B200_REQUIRE(batch <= B200_NOALLOC_MAX_BATCH,
                "conv1_wgrad_noalloc: batch %d exceeds the built-in scratch (max %d samples); use b200_conv1_wgrad "
                "with a caller-provided scratch buffer instead", batch, B200_NOALLOC_MAX_BATCH);

@@ -222,48 +222,6 @@ conv2_wgrad_simt_kernel(const float* __restrict__ dp, const uint8_t* __restrict_
   if (ig == 0) dst[W2_ELEMS + o] = accb;
 }
 
-// materialise dY [B][24][24][64] for the TMA-fed tensor-core backward kernels.  Optionally also
-// produces per-block partial sums of dp per channel (= conv2's bias gradient: every non-zero of dY
-// is an element of dp) in db_part[block][64].
-__global__ void __launch_bounds__(256)
-unpool_dense_kernel(const float* __restrict__ dp, const uint8_t* __restrict__ amax, float* __restrict__ dy, int batch,
-                    float* __restrict__ db_part, float* __restrict__ db_gpart, unsigned int* __restrict__ counters) {
-  __shared__ float4 red[256];
-  pdl_trigger();
-  pdl_wait();
-  const size_t n4 = (size_t)batch * HP * WP * (C2 / 4);
-  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-  // gridDim.x * 256 is a multiple of 16, so a thread always sees the same channel quad
-  for (size_t e4 = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e4 < n4; e4 += (size_t)gridDim.x * blockDim.x) {
-    const int oq = (int)(e4 % (C2 / 4));
-    const size_t win = e4 / (C2 / 4);
-    const int pw = (int)(win % WP), ph = (int)((win / WP) % HP), b = (int)(win / (WP * HP));
-    const float4 d = reinterpret_cast<const float4*>(dp)[e4];
-    const uchar4 a = reinterpret_cast<const uchar4*>(amax)[e4];
-    acc.x += d.x; acc.y += d.y; acc.z += d.z; acc.w += d.w;
-#pragma unroll
-    for (int s = 0; s < 4; ++s) {
-      float4 v = make_float4(a.x == s ? d.x : 0.f, a.y == s ? d.y : 0.f, a.z == s ? d.z : 0.f, a.w == s ? d.w : 0.f);
-      const int y = 2 * ph + (s >> 1), x = 2 * pw + (s & 1);
-      reinterpret_cast<float4*>(dy)[(((size_t)b * H2 + y) * W2 + x) * (C2 / 4) + oq] = v;
-    }
-  }
-  if (db_part) {
-    red[threadIdx.x] = acc;
-    __syncthreads();
-    if (threadIdx.x < 16) {
-      float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-      for (int k = 0; k < 16; ++k) {
-        const float4 r = red[threadIdx.x + 16 * k];
-        t.x += r.x; t.y += r.y; t.z += r.z; t.w += r.w;
-      }
-      reinterpret_cast<float4*>(db_part + (size_t)blockIdx.x * C2)[threadIdx.x] = t;
-    }
-    if (db_gpart) group_reduce_rows(db_part, C2, C2, db_gpart, counters);
-  }
-}
-
 static int sm_count() { return b200_sm_count(); }
 
 extern "C" int b200_conv2_fwd_simt(const float* a1, const float* w, const float* bias, const void* ctrl,
@@ -309,35 +267,6 @@ extern "C" int b200_conv2_wgrad_simt(const float* dp, const uint8_t* amax, const
   b200_count_launch();
   if (dw) b200_launch_reduce_partials(dw, part, W2_ELEMS, grid, CONV2_PART, s);
   if (db) b200_launch_reduce_partials(db, part + W2_ELEMS, C2, grid, CONV2_PART, s);
-  B200_LAUNCH_CHECK();
-  return B200_OK;
-}
-
-// db_part: scratch of b200_unpool_parts() * 64 floats and db [64], or both NULL to skip the bias gradient
-extern "C" int b200_unpool_parts(void) { return 2 * sm_count(); }
-extern "C" int b200_unpool_nparts(int batch) {  // partial rows actually written for this batch
-  const size_t n4 = (size_t)batch * HP * WP * (C2 / 4);
-  return (int)min((size_t)(2 * sm_count()), (n4 + 255) / 256);
-}
-extern "C" int b200_unpool_dense(const float* dp, const uint8_t* amax, float* dy, float* db_part, float* db, int batch,
-                                 void* stream) {
-  B200_REQUIRE(db == nullptr || db_part != nullptr, "unpool_dense: db needs the db_part scratch");
-  const size_t n4 = (size_t)batch * HP * WP * (C2 / 4);
-  const int grid = (int)min((size_t)(2 * sm_count()), (n4 + 255) / 256);
-  cudaStream_t s = (cudaStream_t)stream;
-  B200_CHECK(b200_launch(unpool_dense_kernel, dim3(grid), dim3(256), 0, s, dp, amax, dy, batch, db_part, (float*)nullptr,
-                         (unsigned int*)nullptr));
-  b200_count_launch();
-  if (db) b200_launch_reduce_partials(db, db_part, C2, grid, C2, s);
-  B200_LAUNCH_CHECK();
-  return B200_OK;
-}
-int b200_unpool_dense_grouped(const float* dp, const uint8_t* amax, float* dy, float* db_part, float* db_gpart,
-                              unsigned int* counters, int batch, cudaStream_t s) {
-  B200_REQUIRE(db_part && db_gpart && counters, "unpool_dense_grouped: bad arguments");
-  B200_CHECK(b200_launch(unpool_dense_kernel, dim3(b200_unpool_nparts(batch)), dim3(256), 0, s, dp, amax, dy, batch, db_part,
-                         db_gpart, counters));
-  b200_count_launch();
   B200_LAUNCH_CHECK();
   return B200_OK;
 }

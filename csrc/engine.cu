@@ -114,25 +114,18 @@ int enqueue_forward(Engine* E, const uint8_t* images, const uint8_t* labels, con
                     int batch, bool train, cudaStream_t s) {
   const B200EngineConfig& c = E->cfg;
   float* P = E->P;
-  // draft path (B200_TC bit 128, off by default): conv1 inside conv2's producer warps, one kernel for both
-  const bool fused12 = (E->use_tc & B200_TC_CONV12_V4) && (E->use_tc & B200_TC_CONV2_FWD) && (E->use_tc & B200_TC_CONV2_V3);
-  if (fused12)
-    TRYM(b200_conv12_fwd_tc4(images, idx, ctrl, P + c.offsets[0], P + c.offsets[1], E->a1, P + c.offsets[2],
+  if (E->use_tc & B200_TC_CONV2_FWD) {
+    // conv1 is computed inside conv2's producer warps: one kernel from uint8 images to the pooled activation
+    TRYM(b200_conv12_fwd_tc(images, idx, ctrl, P + c.offsets[0], P + c.offsets[1], E->a1, P + c.offsets[2],
                              P + c.offsets[3], E->pooled, E->amax, batch, s), s);
-  else
+  } else {
     TRYM(b200_conv1_fwd(images, idx, ctrl, P + c.offsets[0], P + c.offsets[1], E->a1, batch, s), s);
-  if (fused12) {}
-  else if ((E->use_tc & B200_TC_CONV2_FWD) && (E->use_tc & B200_TC_CONV2_V3))
-    TRYM(b200_conv2_fwd_tc3(E->a1, P + c.offsets[2], P + c.offsets[3], ctrl, E->pooled, E->amax, batch, s), s);
-  else if ((E->use_tc & B200_TC_CONV2_FWD) && (E->use_tc & B200_TC_CONV2_V2))
-    TRYM(b200_conv2_fwd_tc2(E->a1, P + c.offsets[2], P + c.offsets[3], ctrl, E->pooled, E->amax, batch, s), s);
-  else if (E->use_tc & B200_TC_CONV2_FWD)
-    TRYM(b200_conv2_fwd_tc(E->a1, P + c.offsets[2], P + c.offsets[3], ctrl, E->pooled, E->amax, batch, s), s);
-  else
     TRYM(b200_conv2_fwd_simt(E->a1, P + c.offsets[2], P + c.offsets[3], ctrl, E->pooled, E->amax, batch, s), s);
+  }
   const int splits = fc1_splits(batch);
+  const int fp32 = (E->use_tc & B200_TC_FC1_FP32) ? 1 : 0;
   if (E->use_tc & B200_TC_FC1_FWD)
-    TRYM(b200_tc_gemm(E->pooled, P + c.offsets[4], E->fc1_part, batch, FC1_OUT, FC1_IN, 0, 0, splits, 0, nullptr, 0.f, s), s);
+    TRYM(b200_tc_gemm_ex(E->pooled, P + c.offsets[4], E->fc1_part, batch, FC1_OUT, FC1_IN, 0, 0, splits, 0, nullptr, 0.f, fp32, s), s);
   else
     TRYM(b200_sgemm(E->pooled, FC1_IN, 1, P + c.offsets[4], 1, FC1_IN, E->fc1_part, batch, FC1_OUT, FC1_IN, splits, 0,
                    nullptr, 0.f, s), s);
@@ -142,21 +135,22 @@ int enqueue_forward(Engine* E, const uint8_t* images, const uint8_t* labels, con
   return B200_OK;
 }
 
+// One optimizer step.  Stream structure (events = graph edges when captured):
+//   s  (critical path): forward -> fc1 dgrad -> conv2 dgrad -> conv1 wgrad -> [join] -> end-of-step kernel
+//   br0 (after head)  : head wgrad -> fc1 wgrad -> [after fc1 dgrad] fc-bucket update
+//   br1 (after fc1 dgrad): conv2 wgrad -> conv2 half of the conv bucket (partial rows -> gradient, and with data
+//                       parallelism the cross-GPU all-reduce of it) under conv2 dgrad / conv1 wgrad
+// The end-of-step kernel is left with conv1's 1.3 KB of gradient, the conv bucket's Adadelta and the step counter.
 int enqueue_train(Engine* E, const uint8_t* images, const uint8_t* labels, const int32_t* idx, int batch,
                   int advance, cudaStream_t s) {
   const B200EngineConfig& c = E->cfg;
   float* P = E->P;
   float* G = E->G[0];
   const float drop1_scale = E->dropout ? 1.0f / (1.0f - P_DROP1) : 1.0f;
-  // fc1 dgrad can scatter straight into dY when both it and the conv2 backward run on tensor cores and
-  // the step's last kernel reduces the bias-gradient partials
-  // (opt-in: measured 141 us/step against 137 us with the separate, fully coalesced un-pool kernel)
-  static const bool want_fused_unpool = getenv("B200_FUSE_UNPOOL") && atoi(getenv("B200_FUSE_UNPOOL")) == 1;
-  const bool fuse_unpool = want_fused_unpool && (E->use_tc & B200_TC_FC1_BWD) && (E->use_tc & B200_TC_CONV2_BWD) &&
-                           (E->hooks.bucket_ready != nullptr || !E->defer_update);
+  const int fp32 = (E->use_tc & B200_TC_FC1_FP32) ? 1 : 0;
   TRY(enqueue_forward(E, images, labels, idx, E->ctrl, batch, true, s));
   // Fork: the head's weight gradients and the fc1 wgrad GEMM only feed the optimizer, so they leave the
-  // critical path (fc1 dgrad -> un-pool -> conv2 dgrad -> conv1 wgrad) and run next to it.
+  // critical path and run next to it.
   const bool par = E->branches && E->br[0] != nullptr;
   cudaStream_t sw = par ? E->br[0] : s;
   if (par) {
@@ -164,118 +158,91 @@ int enqueue_train(Engine* E, const uint8_t* images, const uint8_t* labels, const
     B200_CHECK(cudaStreamWaitEvent(sw, E->ev_head, 0));
   }
   // fc1: dp = (dh . W1) * (pooled > 0 ? 1/(1-p1) : 0)   -- critical path, enqueued first
-  if (E->use_tc & B200_TC_FC1_BWD) {
-    if (fuse_unpool)  // dgrad writes the dense dY (and conv2 bias-gradient partials) itself
-      TRYM(b200_fc1_dgrad_unpool_tc(E->dh, P + c.offsets[4], E->pooled, E->amax, E->dy, E->db_part, batch, drop1_scale, s), s);
-    else
-      TRYM(b200_tc_gemm(E->dh, P + c.offsets[4], E->dp, batch, FC1_IN, FC1_OUT, 0, 1, 1, 1, E->pooled, drop1_scale, s), s);
-  } else {
+  if (E->use_tc & B200_TC_FC1_BWD)
+    TRYM(b200_tc_gemm_ex(E->dh, P + c.offsets[4], E->dp, batch, FC1_IN, FC1_OUT, 0, 1, 1, 1, E->pooled, drop1_scale, fp32, s), s);
+  else
     TRYM(b200_sgemm(E->dh, FC1_OUT, 1, P + c.offsets[4], FC1_IN, 1, E->dp, batch, FC1_IN, FC1_OUT, 1, 1, E->pooled,
                    drop1_scale, s), s);
-  }
   // dW2, db2, db1, mean loss; fc1: dW1[128][9216] = dh^T . pooled
   TRYM(b200_head_wgrad(E->h, E->dlogits, E->dh, E->loss_i, batch, G + c.offsets[6], G + c.offsets[7], G + c.offsets[5],
                       E->loss_scalar, E->ctrl, E->loss_ring, B200_LOSS_RING, E->loss_ring_host_dev, sw), sw);
   if (E->use_tc & B200_TC_FC1_BWD)
-    TRYM(b200_tc_gemm(E->dh, E->pooled, G + c.offsets[4], FC1_OUT, FC1_IN, batch, 1, 1, 1, 0, nullptr, 0.f, sw), sw);
+    TRYM(b200_tc_gemm_ex(E->dh, E->pooled, G + c.offsets[4], FC1_OUT, FC1_IN, batch, 1, 1, 1, 0, nullptr, 0.f, fp32, sw), sw);
   else
     TRYM(b200_sgemm(E->dh, 1, FC1_OUT, E->pooled, FC1_IN, 1, G + c.offsets[4], FC1_OUT, FC1_IN, batch, 1, 0, nullptr,
                    0.f, sw), sw);
-  const bool own_update = !E->hooks.bucket_ready && !E->defer_update;
-  bool fc_updated = false;
+  const bool ddp = E->hooks.bucket_ready != nullptr;
+  const bool own_update = !ddp && !E->defer_update;
+  bool fc_updated = false, fc_pending = false;
   if (par) {
-    B200_CHECK(cudaEventRecord(E->ev_fcw, sw));
+    B200_CHECK(cudaEventRecord(E->ev_fcd, s));  // fc1 dgrad done: dp is ready, the old fc1.weight has been read
     if (E->defer_update) {
-      B200_CHECK(cudaStreamWaitEvent(s, E->ev_fcw, 0));  // the caller reduces/updates: the fc bucket must be complete
+      B200_CHECK(cudaEventRecord(E->ev_fcw, sw));  // the caller reduces/updates: the fc bucket must be complete
+      fc_pending = true;
     } else {
       // The fc bucket (98 % of the parameters) is complete on the branch.  Its update -- Adadelta on one
       // GPU, the fused all-reduce + Adadelta kernel with data parallelism -- stays on the branch, under
       // the conv backward; it may only start once fc1 dgrad has read the old fc1.weight.
-      B200_CHECK(cudaEventRecord(E->ev_fcd, s));
       B200_CHECK(cudaStreamWaitEvent(sw, E->ev_fcd, 0));
       if (own_update) TRYM(b200_adadelta(P, G, E->V, E->U, c.bucket_begin[1], E->ctrl, 0.9f, 1e-6f, -1, nullptr, sw), sw);
       else TRYM(E->hooks.bucket_ready(E, 0, sw), sw);
       B200_CHECK(cudaEventRecord(E->ev_fcu, sw));
       fc_updated = true;
     }
-  } else if (E->hooks.bucket_ready) {
+  } else if (ddp) {
     TRYM(E->hooks.bucket_ready(E, 0, s), s);  // bucket 0 (fc1.*, fc2.*) is complete here
+    fc_updated = true;
   }
-  // With data-parallel hooks the conv-bucket gradients are left as per-CTA partials: the step's last
-  // kernel reduces them, all-reduces, and applies Adadelta in one go (fin).
-  const bool fuse = E->hooks.bucket_ready != nullptr || !E->defer_update;
+  // ---- conv2 backward: wgrad on its own branch next to dgrad; both read (dp, argmax) directly
   const long b1 = c.bucket_begin[1];
-  float* dw2 = fuse ? nullptr : G + c.offsets[2];
-  float* db2 = fuse ? nullptr : G + c.offsets[3];
+  cudaStream_t sc = par ? E->br[1] : s;
+  if (par) B200_CHECK(cudaStreamWaitEvent(sc, E->ev_fcd, 0));
   int np2 = 0;
-  bool c2w_pending = false;
-  if (E->use_tc & B200_TC_CONV2_BWD) {
-    // Draft path (B200_TC bit 64, off by default): the v4 dgrad expands (dp, amax) itself, so only conv2 wgrad
-    // still needs the dense dY and the un-pool kernel moves to the wgrad branch, off the critical path.
-    const bool v4 = (E->use_tc & B200_TC_CONV2_V4) && (E->use_tc & B200_TC_CONV2_V2) && !fuse_unpool;
-    // Fork: conv2 wgrad and conv2 dgrad both read dY; wgrad runs beside dgrad / conv1 wgrad
-    cudaStream_t sc = par ? E->br[1] : s;
-    cudaStream_t su = (v4 && par) ? sc : s;  // stream of the un-pool kernel
-    if (par && v4) {
-      B200_CHECK(cudaEventRecord(E->ev_dy, s));
-      B200_CHECK(cudaStreamWaitEvent(sc, E->ev_dy, 0));
-    }
-    if (!fuse_unpool) {
-      if (fuse) TRYM(b200_unpool_dense_grouped(E->dp, E->amax, E->dy, E->db_part, E->db_gpart, E->db_cnt, batch, su), su);
-      else TRYM(b200_unpool_dense(E->dp, E->amax, E->dy, E->db_part, db2, batch, su), su);
-    }
-    if (par && !v4) {
-      B200_CHECK(cudaEventRecord(E->ev_dy, s));
-      B200_CHECK(cudaStreamWaitEvent(sc, E->ev_dy, 0));
-    }
+  for (int pass = 0; pass < 2; ++pass) {
     // with branches the critical-path kernel (dgrad) is enqueued first so that it gets the SMs first
-    for (int pass = 0; pass < 2; ++pass) {
-      const bool do_wgrad = (pass == 0) != par;
-      if (E->use_tc & B200_TC_CONV2_V2) {
-        if (do_wgrad) TRYM(b200_conv2_wgrad_tc2(E->dy, E->a1, E->c2_part, dw2, batch, sc), sc);
-        else if (v4) TRYM(b200_conv2_dgrad_tc4(E->dp, E->amax, P + c.offsets[2], E->a1, E->da1, batch, s), s);
-        else if (E->use_tc & B200_TC_CONV2_V3) TRYM(b200_conv2_dgrad_tc3(E->dy, P + c.offsets[2], E->a1, E->da1, batch, s), s);
-        else TRYM(b200_conv2_dgrad_tc2(E->dy, P + c.offsets[2], E->a1, E->da1, batch, s), s);
+    const bool do_wgrad = (pass == 0) != par;
+    if (E->use_tc & B200_TC_CONV2_BWD) {
+      if (do_wgrad) {
+        TRYM(b200_conv2_wgrad_tc(E->dp, E->amax, E->a1, E->c2_part, nullptr, nullptr, batch, sc), sc);
+        np2 = b200_conv2_wgrad_tc_parts(batch);
       } else {
-        if (do_wgrad) TRYM(b200_conv2_wgrad_tc(E->dy, E->a1, E->c2_part, dw2, batch, sc), sc);
-        else TRYM(b200_conv2_dgrad_tc(E->dy, P + c.offsets[2], E->a1, E->da1, batch, s), s);
+        TRYM(b200_conv2_dgrad_tc(E->dp, E->amax, P + c.offsets[2], E->a1, E->da1, batch, s), s);
+      }
+    } else {
+      if (do_wgrad) {
+        TRYM(b200_conv2_wgrad_simt(E->dp, E->amax, E->a1, E->c2_part, nullptr, nullptr, batch, sc), sc);
+        np2 = min(9 * batch, E->nsm);
+      } else {
+        TRYM(b200_conv2_dgrad_simt(E->dp, E->amax, P + c.offsets[2], E->a1, E->da1, batch, s), s);
       }
     }
-    np2 = min(((E->use_tc & B200_TC_CONV2_V2) ? 3 : 9) * batch, E->nsm);
-    if (par) {
-      B200_CHECK(cudaEventRecord(E->ev_c2w, sc));
-      c2w_pending = true;
-    }
-    if (fuse_unpool)  // partial rows = (128-sample tile, pooled pixel): [ceil(B/128)*144][64]
-      E->fin.seg[1] = {E->db_part, ceil_div(batch, 128) * HP * WP, C2, C2, (int)(c.offsets[3] - b1)};
-    else
-      E->fin.seg[1] = {E->db_gpart, b200_group_count(b200_unpool_nparts(batch)), C2, C2, (int)(c.offsets[3] - b1)};
-  } else {
-    TRYM(b200_conv2_wgrad_simt(E->dp, E->amax, E->a1, E->c2_part, dw2, db2, batch, s), s);
-    TRYM(b200_conv2_dgrad_simt(E->dp, E->amax, P + c.offsets[2], E->a1, E->da1, batch, s), s);
-    np2 = min(9 * batch, E->nsm);
-    E->fin.seg[1] = {E->c2_part + 9 * C2 * C1, np2, 9 * C2 * C1 + C2, C2, (int)(c.offsets[3] - b1)};
   }
-  E->fin.seg[0] = {E->c2_part, np2, 9 * C2 * C1 + C2, 9 * C2 * C1, (int)(c.offsets[2] - b1)};
+  const int c2row = 9 * C2 * C1 + C2;
+  E->fin_c2.seg[0] = {E->c2_part, np2, c2row, 9 * C2 * C1, (int)(c.offsets[2] - b1)};
+  E->fin_c2.seg[1] = {E->c2_part + 9 * C2 * C1, np2, c2row, C2, (int)(c.offsets[3] - b1)};
+  if (ddp) TRYM(E->hooks.bucket_ready(E, 2, sc), sc);  // partial rows -> gradient -> cross-GPU all-reduce
+  else TRYM(b200_reduce_segs(G + b1, E->c2_chunks, E->fin_c2, sc), sc);
+  if (par) B200_CHECK(cudaEventRecord(E->ev_c2w, sc));
+  // ---- conv1 wgrad (critical path), left as group-combined partial rows for the end-of-step kernel
+  const bool fuse = ddp || !E->defer_update;
   if (fuse) {
     TRYM(b200_conv1_wgrad_grouped(images, idx, E->ctrl, E->da1, E->c1_part, E->c1_gpart, E->c1_cnt, batch, s), s);
     const int ng = b200_group_count(2 * batch);
-    E->fin.seg[2] = {E->c1_gpart, ng, 320, 288, (int)(c.offsets[0] - b1)};
-    E->fin.seg[3] = {E->c1_gpart + 288, ng, 320, 32, (int)(c.offsets[1] - b1)};
+    E->fin_c1.seg[0] = {E->c1_gpart, ng, 320, 288, (int)(c.offsets[0] - b1)};
+    E->fin_c1.seg[1] = {E->c1_gpart + 288, ng, 320, 32, (int)(c.offsets[1] - b1)};
   } else {
     TRYM(b200_conv1_wgrad(images, idx, E->ctrl, E->da1, E->c1_part, G + c.offsets[0], G + c.offsets[1], batch, s), s);
   }
-  E->fin_valid = fuse;
-  // Join: everything the step's last kernel(s) read must be complete
-  if (c2w_pending) B200_CHECK(cudaStreamWaitEvent(s, E->ev_c2w, 0));
-  if (fc_updated) B200_CHECK(cudaStreamWaitEvent(s, E->ev_fcu, 0));
-  if (E->hooks.bucket_ready) {
-    TRYM(E->hooks.bucket_ready(E, 1, s), s);
+  // Join: everything the step's last kernel reads must be complete
+  if (par) B200_CHECK(cudaStreamWaitEvent(s, E->ev_c2w, 0));
+  if (fc_updated && par) B200_CHECK(cudaStreamWaitEvent(s, E->ev_fcu, 0));
+  if (fc_pending) B200_CHECK(cudaStreamWaitEvent(s, E->ev_fcw, 0));
+  if (ddp) {
     TRYM(E->hooks.step_end(E, advance, s), s);
   } else if (!E->defer_update) {
     // bucket 0 occupies floats [0, bucket_begin[1]) of the flat layout, bucket 1 the rest
-    TRYM(b200_adadelta_finalize(P, G, E->V, E->U, b1, (int)((c.bucket_end[1] - b1) / 256), E->fin, E->ctrl, 0.9f,
-                               1e-6f, advance, E->done_counter, fc_updated, s), s);
+    TRYM(b200_adadelta_finalize(P, G, E->V, E->U, b1, E->conv_chunks, E->c2_chunks, E->fin_c1, E->ctrl, 0.9f, 1e-6f,
+                               advance, E->done_counter, fc_updated, s), s);
   }
   return B200_OK;
 }
@@ -361,6 +328,13 @@ extern "C" int b200_engine_create(const B200EngineConfig* cfg, void** out) {
   E->cfg = *cfg;
   E->use_tc = cfg->use_tc;
   E->nsm = b200_sm_count();
+  // the conv bucket is [conv2.weight | conv2.bias | conv1.weight | conv1.bias] in 256-float chunks (ParamLayout)
+  B200_REQUIRE(cfg->offsets[2] == cfg->bucket_begin[1] && cfg->offsets[3] > cfg->offsets[2] &&
+               cfg->offsets[0] > cfg->offsets[3] && cfg->offsets[1] > cfg->offsets[0] &&
+               (cfg->bucket_end[1] - cfg->bucket_begin[1]) % 256 == 0 && (cfg->offsets[0] - cfg->bucket_begin[1]) % 256 == 0,
+               "engine_create: unexpected conv bucket layout");
+  E->c2_chunks = (int)((cfg->offsets[0] - cfg->bucket_begin[1]) / 256);
+  E->conv_chunks = (int)((cfg->bucket_end[1] - cfg->bucket_begin[1]) / 256);
   const size_t B = (size_t)cfg->max_batch, T = (size_t)cfg->param_floats;
   int r = B200_OK;
 #define A(ptr, count) if (r == B200_OK) r = dev_alloc(E, &(ptr), (count))
@@ -398,11 +372,7 @@ extern "C" int b200_engine_create(const B200EngineConfig* cfg, void** out) {
   A(E->c1_part, 2 * B * 320);
   A(E->c1_gpart, (size_t)b200_group_count(2 * cfg->max_batch) * 320);
   A(E->c1_cnt, (size_t)b200_group_count(2 * cfg->max_batch));
-  A(E->db_gpart, (size_t)b200_group_count(b200_unpool_parts()) * C2);
-  A(E->db_cnt, (size_t)b200_group_count(b200_unpool_parts()));
   A(E->c2_part, (size_t)E->nsm * (9 * C2 * C1 + C2));
-  if (cfg->use_tc & B200_TC_CONV2_BWD) A(E->dy, B * H2 * W2 * C2);
-  A(E->db_part, max((size_t)b200_unpool_parts() * C2, (size_t)ceil_div(cfg->max_batch, 128) * FC1_IN));
   A(E->loss_ring, (size_t)B200_LOSS_RING);
   A(E->loss_scalar, 4);
   A(E->ctrl, 1);
@@ -417,7 +387,7 @@ extern "C" int b200_engine_create(const B200EngineConfig* cfg, void** out) {
   B200_CHECK(cudaHostGetDevicePointer((void**)&E->loss_ring_host_dev, E->loss_ring_host, 0));
   E->branches = !(getenv("B200_NO_BRANCH") && atoi(getenv("B200_NO_BRANCH")) == 1);
   for (int i = 0; i < 2; ++i) B200_CHECK(cudaStreamCreateWithFlags(&E->br[i], cudaStreamNonBlocking));
-  for (cudaEvent_t* e : {&E->ev_head, &E->ev_fcw, &E->ev_fcd, &E->ev_fcu, &E->ev_dy, &E->ev_c2w})
+  for (cudaEvent_t* e : {&E->ev_head, &E->ev_fcw, &E->ev_fcd, &E->ev_fcu, &E->ev_c2w})
     B200_CHECK(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
   const float inv_w = 1.0f / (float)(cfg->world > 0 ? cfg->world : 1);
   TRY(b200_ctrl_set(E->ctrl, 0, cfg->seed, 0, 3, 1.0f, inv_w, nullptr));
@@ -437,7 +407,7 @@ extern "C" int b200_engine_destroy(void* engine) {
   }
   if (E->hooks.destroy) E->hooks.destroy(E);
   for (int i = 0; i < 2; ++i) if (E->br[i]) cudaStreamDestroy(E->br[i]);
-  for (cudaEvent_t e : {E->ev_head, E->ev_fcw, E->ev_fcd, E->ev_fcu, E->ev_dy, E->ev_c2w}) if (e) cudaEventDestroy(e);
+  for (cudaEvent_t e : {E->ev_head, E->ev_fcw, E->ev_fcd, E->ev_fcu, E->ev_c2w}) if (e) cudaEventDestroy(e);
   if (E->copy_stream) {
     cudaStreamDestroy(E->copy_stream);
     for (int i = 0; i < 2; ++i) { cudaEventDestroy(E->ev_copied[i]); cudaEventDestroy(E->ev_consumed[i]); }

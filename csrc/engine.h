@@ -6,26 +6,63 @@
 
 #include "common.cuh"
 
-enum { B200_TC_CONV2_FWD = 1, B200_TC_FC1_FWD = 2, B200_TC_FC1_BWD = 4, B200_TC_CONV2_BWD = 8, B200_TC_CONV2_V2 = 16, B200_TC_CONV2_V3 = 32,
-       B200_TC_CONV2_V4 = 64 /* draft dY-free dgrad (tc_conv2_v4.cu), opt-in only */,
-       B200_TC_CONV12_V4 = 128 /* draft fused conv1+conv2 forward (tc_conv2_v4.cu), opt-in only */ };
+// which layers run on the tcgen05 kernels (B200EngineConfig.use_tc); a cleared bit selects the fp32 CUDA-core kernel
+enum { B200_TC_CONV2_FWD = 1 /* conv1+conv2 forward in one kernel (tc_conv2_v4.cu) */, B200_TC_FC1_FWD = 2,
+       B200_TC_FC1_BWD = 4, B200_TC_CONV2_BWD = 8 /* dgrad + wgrad straight from (dp, argmax): no dense dY */,
+       B200_TC_FC1_FP32 = 16 /* fc1 GEMMs as 3xTF32 split-operand products (fp32-class, the reference's SGEMM accuracy) */ };
 
-// Where the conv bucket's gradients still sit as per-CTA partial sums at the end of backward.  The
-// last kernel of the step (allreduce.cu: finalize_bucket_kernel) reduces them itself, so no separate
-// reduction kernels sit on the critical path.  dst_off: float offset inside the bucket (x256).
-constexpr int FIN_SLICES = 16;  // the finalize kernels run 64 float4 columns x FIN_SLICES row slices per CTA
+// Where conv-bucket gradients still sit as per-CTA partial sums when a backward kernel ends.  The kernels
+// that consume them (adadelta.cu / allreduce.cu) run one CTA per 256-float chunk of the bucket and reduce
+// the partial rows themselves in a fixed order, so no separate reduction launches sit on the critical
+// path.  dst_off: float offset of the segment inside the bucket (a multiple of 256); n: floats per row.
+constexpr int FIN_SLICES = 16;  // those kernels run 64 float4 columns x (blockDim/64 <= FIN_SLICES) row slices per CTA
 struct FinalizeSegs {
-  struct Seg { const float* src; int nparts, stride, n, dst_off; } seg[4];
+  struct Seg { const float* src; int nparts, stride, n, dst_off; } seg[2];
 };
+#ifdef __CUDACC__
+// sum over the partial rows of the segment(s) covering floats [off + 4*col, +4) of the bucket; every thread of
+// the CTA calls this (col = threadIdx & 63, slice = threadIdx >> 6), the total is returned to slice 0
+__device__ __forceinline__ float4 reduce_partial_chunk(const FinalizeSegs& segs, int off, float4 (*red)[64]) {
+  const int col = threadIdx.x & 63, slice = threadIdx.x >> 6, nsl = blockDim.x >> 6;
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+  for (int k = 0; k < 2; ++k) {
+    const FinalizeSegs::Seg sg = segs.seg[k];
+    const int e = off - sg.dst_off + 4 * col;
+    if (sg.src && e >= 0 && e < sg.n) {
+#pragma unroll 8
+      for (int p = slice; p < sg.nparts; p += nsl) {
+        const float4 v = __ldcg(reinterpret_cast<const float4*>(sg.src + (size_t)p * sg.stride + e));
+        acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+      }
+    }
+  }
+  red[slice][col] = acc;
+  __syncthreads();
+  float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (slice == 0) {
+    t = red[0][col];
+    for (int q = 1; q < nsl; ++q) { const float4 v = red[q][col]; t.x += v.x; t.y += v.y; t.z += v.z; t.w += v.w; }
+  }
+  return t;
+}
+#endif
 
-// adadelta.cu: single-GPU end of step = partial reduction of the conv bucket + Adadelta on everything
-int b200_adadelta_finalize(float* p, float* g, float* v, float* u, long b1_off, int nchunks, const FinalizeSegs& segs,
-                           void* ctrl, float rho, float eps, int advance, unsigned int* done_counter, bool bucket0_done,
-                           cudaStream_t s);
+// adadelta.cu
+// conv2's half of the conv bucket on one GPU: partial rows -> gradient buffer (chunks [0, nchunks) of dst)
+int b200_reduce_segs(float* dst, int nchunks, const FinalizeSegs& segs, cudaStream_t s);
+// single-GPU end of step: chunks [0, first_partial) of the conv bucket take their gradient from g, chunks
+// [first_partial, nchunks) reduce `segs` first; then Adadelta on the conv bucket (and on the fc bucket unless
+// bucket0_done), and the step counter advances
+int b200_adadelta_finalize(float* p, float* g, float* v, float* u, long b1_off, int nchunks, int first_partial,
+                           const FinalizeSegs& segs, void* ctrl, float rho, float eps, int advance,
+                           unsigned int* done_counter, bool bucket0_done, cudaStream_t s);
 
 struct Engine;
 struct EngineHooks {
-  // called (inside the step's stream order / graph capture) when a gradient bucket is complete
+  // called (inside the step's stream order / graph capture) when gradients are complete:
+  //   bucket 0 = fc bucket (in the gradient buffer), 2 = conv2's part of the conv bucket (as partial rows, fin_c2);
+  //   the rest of the conv bucket (conv1, fin_c1) is handled by step_end
   int (*bucket_ready)(Engine*, int bucket, cudaStream_t) = nullptr;
   // called once per step after the last bucket: joins side streams, advances the control block
   int (*step_end)(Engine*, int advance, cudaStream_t) = nullptr;
@@ -46,9 +83,9 @@ struct Engine {
   uint8_t *stage_img = nullptr, *stage_lbl = nullptr;
   float *a1 = nullptr, *da1 = nullptr, *pooled = nullptr, *dp = nullptr, *h = nullptr, *dh = nullptr,
         *dlogits = nullptr, *loss_i = nullptr, *logp = nullptr, *fc1_part = nullptr, *c1_part = nullptr,
-        *c2_part = nullptr, *dy = nullptr, *db_part = nullptr, *loss_ring = nullptr, *loss_scalar = nullptr;
-  float *c1_gpart = nullptr, *db_gpart = nullptr;      // group-combined partial rows (common.cuh: group_reduce_rows)
-  unsigned int *c1_cnt = nullptr, *db_cnt = nullptr;   // their arrival counters
+        *c2_part = nullptr, *loss_ring = nullptr, *loss_scalar = nullptr;
+  float* c1_gpart = nullptr;      // group-combined partial rows of conv1 wgrad (common.cuh: group_reduce_rows)
+  unsigned int* c1_cnt = nullptr;  // their arrival counters
   uint8_t* amax = nullptr;
   int* correct_i = nullptr;
   B200Ctrl *ctrl = nullptr, *ctrl_eval = nullptr;
@@ -67,9 +104,9 @@ struct Engine {
   // events, so the whole step is still one capturable graph): br[0] = head wgrad, fc1 wgrad and the
   // fc bucket's Adadelta, br[1] = conv2 wgrad.
   cudaStream_t br[2] = {nullptr, nullptr};
-  cudaEvent_t ev_head = nullptr, ev_fcw = nullptr, ev_fcd = nullptr, ev_fcu = nullptr, ev_dy = nullptr, ev_c2w = nullptr;
+  cudaEvent_t ev_head = nullptr, ev_fcw = nullptr, ev_fcd = nullptr, ev_fcu = nullptr, ev_c2w = nullptr;
   bool branches = true;
   EngineHooks hooks;
-  FinalizeSegs fin{};       // filled by enqueue_train when fin_valid
-  bool fin_valid = false;
+  FinalizeSegs fin_c2{}, fin_c1{};  // partial rows of conv2 / conv1 wgrad, filled by enqueue_train
+  int c2_chunks = 0, conv_chunks = 0;  // 256-float chunks of conv2.{weight,bias} / of the whole conv bucket
 };

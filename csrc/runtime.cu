@@ -12,11 +12,52 @@
 static thread_local char g_err[1024] = "";
 static std::atomic<long long> g_launches{0};
 
+static std::mutex g_fault_mu;
+static std::vector<CommFault*> g_fault_records;
+
+void b200_register_fault_record(CommFault* p) {
+  std::lock_guard<std::mutex> lock(g_fault_mu);
+  g_fault_records.push_back(p);
+}
+void b200_unregister_fault_record(CommFault* p) {
+  std::lock_guard<std::mutex> lock(g_fault_mu);
+  for (size_t i = 0; i < g_fault_records.size(); ++i)
+    if (g_fault_records[i] == p) { g_fault_records.erase(g_fault_records.begin() + i); break; }
+}
+
+// text of the first complete cross-GPU barrier fault record, or 0 characters
+static int fault_text(char* buf, size_t len) {
+  std::lock_guard<std::mutex> lock(g_fault_mu);
+  for (CommFault* f : g_fault_records) {
+    if (!f || *(volatile unsigned int*)&f->valid != 2u) continue;
+    static const char* kinds[] = {"entry barrier", "exit barrier", "chunk owner waiting for contributions"};
+    return snprintf(buf, len,
+                    "cross-GPU barrier timed out: rank %d of %d waited %.1f s for rank %d (channel %d, %s, CTA %d, step "
+                    "%llu, expected token %u, last seen %u) -- that peer exited, hung, or is more than "
+                    "B200_COMM_TIMEOUT_MS behind", f->rank, f->world, (double)f->waited_ns * 1e-9, f->peer, f->channel,
+                    kinds[f->kind >= 0 && f->kind < 3 ? f->kind : 0], f->block, f->step, f->expected, f->seen);
+  }
+  return 0;
+}
+
 void b200_set_error(const char* fmt, ...) {
   va_list ap;
   va_start(ap, fmt);
-  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  int n = vsnprintf(g_err, sizeof(g_err), fmt, ap);
   va_end(ap);
+  if (n < 0) n = 0;
+  if ((size_t)n >= sizeof(g_err) - 8) return;
+  char extra[512];
+  if (fault_text(extra, sizeof(extra)) > 0) snprintf(g_err + n, sizeof(g_err) - n, " [%s]", extra);
+}
+
+// the pending barrier-fault message (empty string when no barrier has timed out); for hosts that see a CUDA error
+// from some other library first (e.g. torch) and want to know whether a lost peer is behind it
+extern "C" const char* b200_comm_fault_message(void) {
+  static thread_local char buf[512];
+  buf[0] = 0;
+  fault_text(buf, sizeof(buf));
+  return buf;
 }
 
 void b200_count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }

@@ -16,6 +16,19 @@
 #include "common.cuh"
 #include "symm.h"
 
+CommFault* symm_fault_record(SymmArena* a) {
+  if (a->fault_dev) return a->fault_dev;
+  void* h = nullptr;
+  if (cudaHostAlloc(&h, sizeof(CommFault), cudaHostAllocMapped) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+  memset(h, 0, sizeof(CommFault));
+  void* d = nullptr;
+  if (cudaHostGetDevicePointer(&d, h, 0) != cudaSuccess) { cudaGetLastError(); cudaFreeHost(h); return nullptr; }
+  a->fault_host = (CommFault*)h;
+  a->fault_dev = (CommFault*)d;
+  b200_register_fault_record(a->fault_host);
+  return a->fault_dev;
+}
+
 extern "C" int b200_symm_handle_bytes(void) { return (int)sizeof(cudaIpcMemHandle_t); }
 extern "C" int b200_symm_flag_bytes(void) { return SYMM_FLAG_BYTES; }
 
@@ -111,6 +124,7 @@ extern "C" int b200_symm_destroy(void* arena) {
   for (int q = 0; q < a->world; ++q)
     if (a->opened[q]) cudaIpcCloseMemHandle(a->peer[q]);
   if (a->owns[a->rank]) cudaFree(a->peer[a->rank]);
+  if (a->fault_host) { b200_unregister_fault_record(a->fault_host); cudaFreeHost(a->fault_host); }
   delete a;
   return B200_OK;
 }

@@ -6,9 +6,18 @@
 //     fc1 dgrad    D[B][9216]   = dh[B][128]   . W1[128][9216]      (K-major, N-major) + mask epilogue
 // (mnist_ddp.py:57 and its backward).
 //
-// One CTA computes one 128 x BN tile over its K range: warp 0 = TMA producer, warp 1 = MMA issuer
-// (one elected lane) and TMEM owner, warps 2-5 = epilogue (one TMEM sub-partition each).  A 4-deep
-// mbarrier ring of 32-wide K blocks decouples TMA from the tensor core.
+// One CTA computes one 128 x BN tile over its K range: one TMA producer warp, one MMA issuer warp (one
+// elected lane; TMEM owner) and 8 epilogue warps (two per TMEM sub-partition).  An mbarrier ring of 32-wide
+// K blocks decouples TMA from the tensor core.
+//
+// SPLIT = true is the fp32-class variant ("3xTF32"): the reference runs fc1 as an fp32 SGEMM
+// (torch.backends.cuda.matmul.allow_tf32 = False), and a single TF32 pass keeps only 10 mantissa
+// bits of each operand.  Every operand x is split into hi = x with its 13 low mantissa bits cleared (exactly
+// representable in TF32) and lo = x - hi (exact in fp32, |lo| < 2^-10 |x|), and the product is accumulated as
+// hi*hi + hi*lo + lo*hi into the same TMEM accumulator; the dropped terms are O(2^-20) relative.  The split is
+// done on chip: while the mainloop runs, the (otherwise idle) epilogue warps read each TMA-written stage,
+// overwrite it with hi and write lo to a second tile at the same swizzled offsets, then hand the stage to the
+// MMA warp (fence.proxy.async + mbarrier).  Nothing extra is read from or written to global memory.
 #include <map>
 #include <mutex>
 #include <tuple>
@@ -61,22 +70,23 @@ int encode(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, c
 
 namespace {
 
-constexpr int BM = 128, BK = 32, STAGES = 4;
+constexpr int BM = 128, BK = 32;
 constexpr int A_BYTES = BM * BK * 4;  // 16 KiB
+__host__ __device__ constexpr int stages_for(bool split) { return split ? 3 : 4; }
 
-template <int BN, bool A_MN, bool B_MN, int EPI>
-__global__ void __launch_bounds__(EPI == 2 ? 192 : 320, 1)
+template <int BN, bool A_MN, bool B_MN, int EPI, bool SPLIT>
+__global__ void __launch_bounds__(320, 1)
 tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
                float* __restrict__ D, int M, int N, int nkb_total, int kb_per_split, const float* __restrict__ aux,
-               float scale, const uint8_t* __restrict__ amax, float* __restrict__ dy, float* __restrict__ db_part) {
+               float scale) {
+  constexpr int STAGES = stages_for(SPLIT);
   constexpr int B_BYTES = BN * BK * 4;
-  constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  constexpr int HI_BYTES = A_BYTES + B_BYTES;                 // what TMA writes per stage
+  constexpr int STAGE_BYTES = SPLIT ? 2 * HI_BYTES : HI_BYTES;  // SPLIT: [A hi | B hi | A lo | B lo]
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);  // SW128 needs 1 KiB alignment
-  __shared__ __align__(8) uint64_t full_bar[STAGES], empty_bar[STAGES], tmem_full_bar;
+  __shared__ __align__(8) uint64_t full_bar[STAGES], empty_bar[STAGES], split_bar[STAGES], tmem_full_bar;
   __shared__ uint32_t tmem_base_smem;
-  __shared__ float tr_s[EPI == 2 ? 4 : 1][EPI == 2 ? 32 : 1][33];  // EPI 2: per-warp transpose tile (row -> channel owner)
-  __shared__ float cs_s[EPI == 2 ? 4 : 1][EPI == 2 ? BN : 1];       //        per-warp column sums of the CTA tile
 
   // Roles by warp: the TMA producer and the MMA issuer get the two HIGHEST warp ids of the CTA (the warp
   // arbiter favours high ids, and each then owns an SM sub-partition's top priority); the epilogue warps are
@@ -92,7 +102,9 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&mapA);
     tma_prefetch_desc(&mapB);
-    for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); mbar_init(&split_bar[s], nwarps - 2);
+    }
     mbar_init(&tmem_full_bar, 1);
     fence_barrier_init();
   }
@@ -111,7 +123,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
         mbar_wait(&empty_bar[s], ((kb / STAGES) & 1) ^ 1);
         uint8_t* sa = smem + s * STAGE_BYTES;
         uint8_t* sb = sa + A_BYTES;
-        if (leader) mbar_expect_tx(&full_bar[s], STAGE_BYTES);
+        if (leader) mbar_expect_tx(&full_bar[s], HI_BYTES);
         const int k0 = (kb0 + kb) * BK;
         if (leader) {
           if (A_MN) tma_load_3d(sa, &mapA, &full_bar[s], 0, k0, m0 / 32);
@@ -127,7 +139,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
       constexpr uint32_t idesc = idesc_tf32(BM, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
       for (int kb = 0; kb < nkb; ++kb) {
         const int s = kb % STAGES;
-        mbar_wait(&full_bar[s], (kb / STAGES) & 1);
+        mbar_wait(SPLIT ? &split_bar[s] : &full_bar[s], (kb / STAGES) & 1);
         tc_fence_after();
         const uint32_t sa = smem_u32(smem + s * STAGE_BYTES), sb = sa + A_BYTES;
 #pragma unroll
@@ -135,14 +147,20 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
           const uint64_t ad = A_MN ? desc_mnmajor(sa + kk * 1024, BK * 128) : desc_kmajor(sa + kk * 32);
           const uint64_t bd = B_MN ? desc_mnmajor(sb + kk * 1024, BK * 128) : desc_kmajor(sb + kk * 32);
           if (leader) umma_tf32(tmem_base, ad, bd, idesc, (kb | kk) != 0);
+          if (SPLIT) {  // + hi.lo + lo.hi: the lo tiles sit HI_BYTES further, same layout
+            const uint64_t al = A_MN ? desc_mnmajor(sa + HI_BYTES + kk * 1024, BK * 128) : desc_kmajor(sa + HI_BYTES + kk * 32);
+            const uint64_t bl = B_MN ? desc_mnmajor(sb + HI_BYTES + kk * 1024, BK * 128) : desc_kmajor(sb + HI_BYTES + kk * 32);
+            if (leader) umma_tf32(tmem_base, ad, bl, idesc, 1u);
+            if (leader) umma_tf32(tmem_base, al, bd, idesc, 1u);
+          }
         }
         if (leader) umma_commit(&empty_bar[s]);  // frees the smem slot once these MMAs have read it
       }
       if (leader) umma_commit(&tmem_full_bar);
     }
   } else {
-    // 4 epilogue warps (EPI 2) or 8: warps w and w+4 share TMEM sub-partition q and take alternate
-    // 32-column chunks of the tile
+    // 8 epilogue warps (or 4): warps w and w+4 share TMEM sub-partition q and take alternate 32-column
+    // chunks of the tile
     const int q = wq;  // TMEM sub-partition this warp may read
     const int h = (warp - 2) >> 2, cstep = 32 * ((nwarps - 2) >> 2);
     const int m = m0 + q * 32 + lane;
@@ -159,6 +177,27 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
       }
     };
     if (EPI == 1) load_aux(h * 32);
+    if (SPLIT) {
+      // operand split, stage by stage, by all epilogue threads: hi = x & ~0x1fff (in place), lo = x - hi
+      const int et = (warp - 2) * 32 + lane, nthr = (nwarps - 2) * 32;
+      for (int kb = 0; kb < nkb; ++kb) {
+        const int s = kb % STAGES;
+        mbar_wait(&full_bar[s], (kb / STAGES) & 1);
+        uint8_t* st = smem + s * STAGE_BYTES;
+#pragma unroll 4
+        for (int o = et * 16; o < HI_BYTES; o += nthr * 16) {
+          const uint4 x = *reinterpret_cast<const uint4*>(st + o);
+          const uint4 hi = make_uint4(x.x & 0xffffe000u, x.y & 0xffffe000u, x.z & 0xffffe000u, x.w & 0xffffe000u);
+          const float4 lo = make_float4(__uint_as_float(x.x) - __uint_as_float(hi.x), __uint_as_float(x.y) - __uint_as_float(hi.y),
+                                        __uint_as_float(x.z) - __uint_as_float(hi.z), __uint_as_float(x.w) - __uint_as_float(hi.w));
+          *reinterpret_cast<uint4*>(st + o) = hi;
+          *reinterpret_cast<float4*>(st + HI_BYTES + o) = lo;
+        }
+        fence_proxy_async();  // generic-proxy stores -> visible to the tensor core's operand reads
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&split_bar[s]);
+      }
+    }
     mbar_wait(&tmem_full_bar, 0);
     tc_fence_after();
 #pragma unroll 1
@@ -171,37 +210,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
         for (int j = 0; j < 8; ++j) acur[j] = anext[j];
         if (c0 + cstep < BN) load_aux(c0 + cstep);
       }
-      if (EPI == 2) {
-        // fc1 dgrad fused with the dropout/ReLU mask, the max-pool scatter and conv2's bias gradient.
-        // Columns n0+c0 .. +31 are 32 consecutive channels of ONE pooled pixel.  The chunk is transposed
-        // through shared memory so that a lane owns a CHANNEL and walks the warp's 32 samples: every
-        // global access below is then one fully coalesced 128-byte (or 32-byte) line per warp, and the
-        // per-channel sum for the bias gradient falls out of the same loop.
-        const int n = n0 + c0;
-#pragma unroll
-        for (int j = 0; j < 32; ++j) tr_s[q][lane][j] = v[j];
-        __syncwarp();
-        float cs = 0.f;
-        if (n < N) {
-          const int hw = n >> 6, cb = (n & 63) + lane, ph = hw / 12, pw = hw - ph * 12;
-          const int rows = min(32, M - (m0 + q * 32));
-#pragma unroll 4
-          for (int r = 0; r < rows; ++r) {
-            const size_t mr = (size_t)(m0 + q * 32 + r);
-            const float pv = aux[mr * N + n + lane];
-            const uint32_t am = amax[mr * N + n + lane];
-            const float val = pv > 0.f ? tr_s[q][r][lane] * scale : 0.f;
-            cs += val;
-            float* dst = dy + ((mr * 24 + 2 * ph) * 24 + 2 * pw) * 64 + cb;
-            dst[0] = am == 0u ? val : 0.f;
-            dst[64] = am == 1u ? val : 0.f;
-            dst[24 * 64] = am == 2u ? val : 0.f;
-            dst[24 * 64 + 64] = am == 3u ? val : 0.f;
-          }
-        }
-        cs_s[q][c0 + lane] = cs;
-        __syncwarp();
-      } else if (m < M) {
+      if (m < M) {
 #pragma unroll
         for (int j = 0; j < 32; j += 4) {
           const int n = n0 + c0 + j;
@@ -216,12 +225,6 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
           }
         }
       }
-    }
-    if (EPI == 2) {
-      asm volatile("bar.sync 1, 128;" ::: "memory");  // the four epilogue warps only
-      const int t = q * 32 + lane;                      // 0..127
-      if (t < BN && n0 + t < N)
-        db_part[(size_t)blockIdx.y * N + n0 + t] = (cs_s[0][t] + cs_s[1][t]) + (cs_s[2][t] + cs_s[3][t]);
     }
   }
   tc_fence_before();
@@ -244,6 +247,7 @@ int get_map(const float* p, int R, int K, int mn, int tile, CUtensorMap* out) {
   MapKey key{p, R, K, mn, tile};
   auto it = g_maps.find(key);
   if (it != g_maps.end()) { *out = it->second; return B200_OK; }
+  if (g_maps.size() >= 256) g_maps.clear();  // bounded: a long-lived host may cycle through many buffers
   CUtensorMap m;
   int r;
   if (!mn) {
@@ -261,40 +265,52 @@ int get_map(const float* p, int R, int K, int mn, int tile, CUtensorMap* out) {
   return B200_OK;
 }
 
-template <int BN, bool A_MN, bool B_MN, int EPI>
+template <int BN, bool A_MN, bool B_MN, int EPI, bool SPLIT>
 int launch(const CUtensorMap& ma, const CUtensorMap& mb, float* D, int M, int N, int nkb, int kbs, int splits,
-           const float* aux, float scale, cudaStream_t s, const uint8_t* amax = nullptr, float* dy = nullptr,
-           float* db_part = nullptr) {
-  constexpr int smem = STAGES * (A_BYTES + BN * BK * 4) + 1024;
+           const float* aux, float scale, cudaStream_t s) {
+  constexpr int smem = stages_for(SPLIT) * (SPLIT ? 2 : 1) * (A_BYTES + BN * BK * 4) + 1024;
   static bool attr = false;
   if (!attr) {
-    B200_CHECK(cudaFuncSetAttribute(tc_gemm_kernel<BN, A_MN, B_MN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    B200_CHECK(cudaFuncSetAttribute(tc_gemm_kernel<BN, A_MN, B_MN, EPI, SPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     attr = true;
   }
   dim3 grid(ceil_div(N, BN), ceil_div(M, BM), splits);
   static const int ew = getenv("B200_GEMM_EW") ? atoi(getenv("B200_GEMM_EW")) : 8;  // epilogue warps: 4 or 8
-  B200_CHECK(b200_launch(tc_gemm_kernel<BN, A_MN, B_MN, EPI>, grid, dim3(EPI == 2 || ew == 4 ? 192 : 320), (size_t)smem, s, ma, mb, D, M, N, nkb, kbs,
-                         aux, scale, amax, dy, db_part));
+  B200_CHECK(b200_launch(tc_gemm_kernel<BN, A_MN, B_MN, EPI, SPLIT>, grid, dim3(ew == 4 ? 192 : 320), (size_t)smem, s, ma, mb, D,
+                         M, N, nkb, kbs, aux, scale));
   b200_count_launch();
   B200_LAUNCH_CHECK();
   return B200_OK;
 }
 
-template <int BN, int EPI>
+template <int BN, int EPI, bool SPLIT>
 int dispatch_major(int a_mn, int b_mn, const CUtensorMap& ma, const CUtensorMap& mb, float* D, int M, int N, int nkb,
                    int kbs, int splits, const float* aux, float scale, cudaStream_t s) {
-  if (!a_mn && !b_mn) return launch<BN, false, false, EPI>(ma, mb, D, M, N, nkb, kbs, splits, aux, scale, s);
-  if (!a_mn && b_mn) return launch<BN, false, true, EPI>(ma, mb, D, M, N, nkb, kbs, splits, aux, scale, s);
-  if (a_mn && b_mn) return launch<BN, true, true, EPI>(ma, mb, D, M, N, nkb, kbs, splits, aux, scale, s);
-  return launch<BN, true, false, EPI>(ma, mb, D, M, N, nkb, kbs, splits, aux, scale, s);
+  if (!a_mn && !b_mn) return launch<BN, false, false, EPI, SPLIT>(ma, mb, D, M, N, nkb, kbs, splits, aux, scale, s);
+  if (!a_mn && b_mn) return launch<BN, false, true, EPI, SPLIT>(ma, mb, D, M, N, nkb, kbs, splits, aux, scale, s);
+  if (a_mn && b_mn) return launch<BN, true, true, EPI, SPLIT>(ma, mb, D, M, N, nkb, kbs, splits, aux, scale, s);
+  return launch<BN, true, false, EPI, SPLIT>(ma, mb, D, M, N, nkb, kbs, splits, aux, scale, s);
+}
+
+template <bool SPLIT>
+int dispatch_tile(int bn, int epi, int a_mn, int b_mn, const CUtensorMap& ma, const CUtensorMap& mb, float* D, int M,
+                  int N, int nkb, int kbs, int splits, const float* aux, float scale, cudaStream_t s) {
+  if (bn == 128) {
+    return epi ? dispatch_major<128, 1, SPLIT>(a_mn, b_mn, ma, mb, D, M, N, nkb, kbs, splits, aux, scale, s)
+               : dispatch_major<128, 0, SPLIT>(a_mn, b_mn, ma, mb, D, M, N, nkb, kbs, splits, aux, scale, s);
+  }
+  return epi ? dispatch_major<64, 1, SPLIT>(a_mn, b_mn, ma, mb, D, M, N, nkb, kbs, splits, aux, scale, s)
+             : dispatch_major<64, 0, SPLIT>(a_mn, b_mn, ma, mb, D, M, N, nkb, kbs, splits, aux, scale, s);
 }
 
 }  // namespace
 
 extern "C" int b200_has_tc(void) { return 1; }
 
-extern "C" int b200_tc_gemm(const float* A, const float* B, float* D, int M, int N, int K, int a_mn, int b_mn,
-                            int splits, int epi, const float* aux, float scale, void* stream) {
+// fp32_class != 0: every operand is split into TF32 hi + lo parts on chip and the product accumulated as
+// hi.hi + hi.lo + lo.hi (see the file header); 0: one TF32 pass
+extern "C" int b200_tc_gemm_ex(const float* A, const float* B, float* D, int M, int N, int K, int a_mn, int b_mn,
+                               int splits, int epi, const float* aux, float scale, int fp32_class, void* stream) {
   B200_REQUIRE(M > 0 && N > 0 && K > 0 && splits > 0, "tc_gemm: bad shape M=%d N=%d K=%d splits=%d", M, N, K, splits);
   B200_REQUIRE(N % 4 == 0, "tc_gemm: N (%d) must be a multiple of 4", N);
   B200_REQUIRE(epi == 0 || (epi == 1 && aux && splits == 1), "tc_gemm: epilogue %d needs aux and splits == 1", epi);
@@ -312,26 +328,11 @@ extern "C" int b200_tc_gemm(const float* A, const float* B, float* D, int M, int
   r = get_map(B, N, K, b_mn, bn, &mb);
   if (r != B200_OK) return r;
   cudaStream_t s = (cudaStream_t)stream;
-  if (bn == 128) {
-    return epi ? dispatch_major<128, 1>(a_mn, b_mn, ma, mb, D, M, N, nkb, kbs, splits, aux, scale, s)
-               : dispatch_major<128, 0>(a_mn, b_mn, ma, mb, D, M, N, nkb, kbs, splits, aux, scale, s);
-  }
-  return epi ? dispatch_major<64, 1>(a_mn, b_mn, ma, mb, D, M, N, nkb, kbs, splits, aux, scale, s)
-             : dispatch_major<64, 0>(a_mn, b_mn, ma, mb, D, M, N, nkb, kbs, splits, aux, scale, s);
+  return fp32_class ? dispatch_tile<true>(bn, epi, a_mn, b_mn, ma, mb, D, M, N, nkb, kbs, splits, aux, scale, s)
+                    : dispatch_tile<false>(bn, epi, a_mn, b_mn, ma, mb, D, M, N, nkb, kbs, splits, aux, scale, s);
 }
 
-// fc1 dgrad + dropout/ReLU mask + max-pool scatter + conv2 bias-gradient partials in one tcgen05 GEMM:
-//   dY[B][24][24][64]  <-  (dh[B][128] . W1[128][9216]) * (pooled > 0 ? scale : 0), routed by amax
-//   db_part[ceil(B/128)][9216] = per-CTA column sums (conv2.bias grad = sum over parts and over the 144 pixels)
-extern "C" int b200_fc1_dgrad_unpool_tc(const float* dh, const float* w1, const float* pooled, const uint8_t* amax,
-                                        float* dy, float* db_part, int batch, float scale, void* stream) {
-  B200_REQUIRE(batch > 0 && dh && w1 && pooled && amax && dy && db_part, "fc1_dgrad_unpool_tc: bad arguments");
-  const int M = batch, N = 9216, K = 128;
-  CUtensorMap ma, mb;
-  int r = get_map(dh, M, K, 0, BM, &ma);
-  if (r != B200_OK) return r;
-  r = get_map(w1, N, K, 1, 128, &mb);
-  if (r != B200_OK) return r;
-  return launch<128, false, true, 2>(ma, mb, nullptr, M, N, ceil_div(K, BK), ceil_div(K, BK), 1, pooled, scale,
-                                     (cudaStream_t)stream, amax, dy, db_part);
+extern "C" int b200_tc_gemm(const float* A, const float* B, float* D, int M, int N, int K, int a_mn, int b_mn,
+                            int splits, int epi, const float* aux, float scale, void* stream) {
+  return b200_tc_gemm_ex(A, B, D, M, N, K, a_mn, b_mn, splits, epi, aux, scale, 0, stream);
 }

@@ -60,13 +60,6 @@ int b200_conv2_dgrad_simt(const float* dp, const uint8_t* amax, const float* w, 
 int b200_conv2_wgrad_parts(void); /* number of partial slots the wgrad kernels need (18496 floats each) */
 int b200_conv2_wgrad_simt(const float* dp, const uint8_t* amax, const float* a1, float* part, float* dw, float* db,
                           int batch, void* stream);
-/* dY[B][24][24][64] from the pooled gradient + argmax; optionally conv2's bias gradient db[64]
- * (db_part: scratch of b200_unpool_parts()*64 floats; pass both or neither) */
-int b200_unpool_parts(void);
-int b200_unpool_nparts(int batch);
-int b200_unpool_dense(const float* dp, const uint8_t* amax, float* dy, float* db_part, float* db, int batch,
-                      void* stream);
-
 /* ---- fp32 SIMT GEMM (mnist_ddp.py:57; SURVEY N6,N11) ------------------------------------------- */
 int b200_sgemm(const float* A, long sam, long sak, const float* B, long sbk, long sbn, float* C, int M, int N, int K,
                int splits, int epi, const float* aux, float scale, void* stream);
@@ -79,36 +72,29 @@ int b200_sgemm(const float* A, long sam, long sak, const float* B, long sbk, lon
  * Host-side set-up (tensor maps) is cached per (pointer, shape). */
 int b200_tc_gemm(const float* A, const float* B, float* D, int M, int N, int K, int a_mn, int b_mn, int splits,
                  int epi, const float* aux, float scale, void* stream);
-/* fc1 dgrad fused with the dropout/ReLU mask, the max-pool scatter (writes the dense dY directly) and
- * per-CTA partial sums of conv2's bias gradient: db_part[ceil(batch/128)][9216] */
-int b200_fc1_dgrad_unpool_tc(const float* dh, const float* w1, const float* pooled, const uint8_t* amax, float* dy,
-                             float* db_part, int batch, float scale, void* stream);
-/* implicit-GEMM conv2 forward with the fused bias+ReLU+pool+dropout epilogue (same outputs as _simt) */
+/* same; fp32_class != 0 selects the 3xTF32 split-operand product (hi.hi + hi.lo + lo.hi, operands split on chip):
+ * fp32-class accuracy for the layers the reference runs as fp32 SGEMM (mnist_ddp.py:46,57) */
+int b200_tc_gemm_ex(const float* A, const float* B, float* D, int M, int N, int K, int a_mn, int b_mn, int splits,
+                    int epi, const float* aux, float scale, int fp32_class, void* stream);
+/* implicit-GEMM conv2 forward from an activation tensor a1[B][26][26][32]: kw taps on the N side (128x192x8 MMAs),
+ * fused bias + ReLU + 2x2 max-pool (2-bit argmax) + dropout epilogue; same outputs as _simt */
 int b200_conv2_fwd_tc(const float* a1, const float* w, const float* bias, const void* ctrl, float* pooled,
                       uint8_t* amax, int batch, void* stream);
-/* second generation: one TMA patch load per (image, half), taps as shifted descriptor views */
-int b200_conv2_fwd_tc2(const float* a1, const float* w, const float* bias, const void* ctrl, float* pooled,
-                       uint8_t* amax, int batch, void* stream);
-int b200_conv2_dgrad_tc2(const float* dy, const float* w, const float* a1, float* da1, int batch, void* stream);
-/* third generation forward: kw taps on the N side (128x192x8 MMAs), kw-sum + pooling by warp shuffles */
-int b200_conv2_fwd_tc3(const float* a1, const float* w, const float* bias, const void* ctrl, float* pooled,
-                       uint8_t* amax, int batch, void* stream);
-/* third generation dgrad: the three kw taps sit on the N side of the MMA (128x96x8), summed by shuffles */
-int b200_conv2_dgrad_tc3(const float* dy, const float* w, const float* a1, float* da1, int batch, void* stream);
-/* DRAFT (compiles, not yet validated on a GPU, never selected by default): conv2 dgrad that expands the pooled
- * gradient dp[B][12][12][64] + arg-max codes in its producer warps instead of reading a dense dY tensor. */
-int b200_conv2_dgrad_tc4(const float* dp, const uint8_t* amax, const float* w, const float* a1, float* da1, int batch,
-                         void* stream);
-/* DRAFT, same status: conv1 (gather + normalise + conv + bias + ReLU) computed inside conv2 forward's producer
- * warps; a1 is still written (the backward pass reads it).  Replaces b200_conv1_fwd + b200_conv2_fwd_tc3. */
-int b200_conv12_fwd_tc4(const uint8_t* images, const int32_t* idx, const void* ctrl, const float* w1, const float* b1,
-                        float* a1, const float* w2, const float* b2, float* pooled, uint8_t* amax, int batch,
+/* conv1 (gather + normalise + conv + bias + ReLU) computed inside that kernel's producer warps: one launch from
+ * the uint8 dataset to the pooled activation; a1 is still written (the backward pass reads it).  The engine's
+ * forward (mnist_ddp.py:50-55). */
+int b200_conv12_fwd_tc(const uint8_t* images, const int32_t* idx, const void* ctrl, const float* w1, const float* b1,
+                       float* a1, const float* w2, const float* b2, float* pooled, uint8_t* amax, int batch,
+                       void* stream);
+/* conv2 backward straight from the pooled gradient dp[B][12][12][64] + argmax codes: the dense dY[B][24][24][64] is
+ * never materialised (producer warps expand it into the swizzled operand tiles).  dgrad applies conv1's ReLU mask.
+ * wgrad: part = scratch of b200_conv2_wgrad_tc_parts(batch) rows of 18496 floats (dW[9][64][32] then db[64]);
+ * dw / db may be NULL when the caller reduces the partial rows itself. */
+int b200_conv2_dgrad_tc(const float* dp, const uint8_t* amax, const float* w, const float* a1, float* da1, int batch,
                         void* stream);
-int b200_conv2_wgrad_tc2(const float* dy, const float* a1, float* part, float* dw, int batch, void* stream);
-/* implicit-GEMM dgrad from the dense dY [B][24][24][64]; epilogue applies conv1's ReLU mask */
-int b200_conv2_dgrad_tc(const float* dy, const float* w, const float* a1, float* da1, int batch, void* stream);
-/* implicit-GEMM wgrad from the dense dY; part as for _simt; the bias gradient comes from b200_unpool_dense */
-int b200_conv2_wgrad_tc(const float* dy, const float* a1, float* part, float* dw, int batch, void* stream);
+int b200_conv2_wgrad_tc_parts(int batch);
+int b200_conv2_wgrad_tc(const float* dp, const uint8_t* amax, const float* a1, float* part, float* dw, float* db,
+                        int batch, void* stream);
 
 /* ---- classifier head (mnist_ddp.py:57-61,71,97-99; SURVEY N7-N10,N22) -------------------------- */
 int b200_head_fused(const float* part, int splits, int batch, const float* b1, const float* w2, const float* b2,
@@ -129,8 +115,8 @@ typedef struct B200EngineConfig {
   int max_batch;        /* largest train or eval batch that will be used */
   int world, rank;
   unsigned long long seed;
-  int use_tc;           /* bit mask: 1 conv2 fwd, 2 fc1 fwd, 4 fc1 bwd, 8 conv2 bwd on tcgen05; 16: patch-view (v2)
-                           conv2 kernels, 32: kw-scatter (v3) dgrad; 0: CUDA-core kernels everywhere */
+  int use_tc;           /* bit mask: 1 conv1+conv2 fwd, 2 fc1 fwd, 4 fc1 bwd, 8 conv2 bwd on tcgen05; 16: fc1 GEMMs as
+                           3xTF32 (fp32-class); 0: fp32 CUDA-core kernels everywhere */
   int train_n, test_n;  /* dataset sizes (samples) */
   long param_floats;    /* ParamLayout.total */
   long offsets[8];      /* conv1.w, conv1.b, conv2.w, conv2.b, fc1.w, fc1.b, fc2.w, fc2.b (floats) */
@@ -201,10 +187,19 @@ int b200_comm_plan_create(void* arena, size_t grad_off, size_t param_off, size_t
 int b200_comm_plan_create_emulated(void** arenas, int world, size_t grad_off, size_t param_off, size_t v_off,
                                    size_t u_off, size_t n_floats, int channel, const void** ctrls, void** plan_out);
 int b200_comm_plan_destroy(void* plan);
+/* single-GPU test harness of the conv-bucket kernels (conv2_reduce + conv_finalize, csrc/allreduce.cu): arenas with
+ * payload [params n][grads n][sq_avg n][acc_delta n][reduced n], n = 19456 (the engine's conv bucket layout) */
+int b200_comm_conv_plan_create_emulated(void** arenas, int world, size_t n_floats, const void** ctrls, void** plan_out);
+int b200_comm_conv_bucket_emulated(void* plan, int mode, const float* const* c2_parts, int np2,
+                                   const float* const* c1_parts, int ng, int advance, unsigned int* counters,
+                                   void* stream);
+/* text of a pending cross-GPU barrier time-out ("rank r waited for rank q ..."), or "" -- see B200_COMM_TIMEOUT_MS */
+const char* b200_comm_fault_message(void);
 /* mode 0 one-shot / 1 two-shot / 2 NVLS two-shot (multimem.ld_reduce + multimem.st; needs a multicast arena); opt 1 = fused 1/W + Adadelta, 0 = averaged all-reduce into param_off;
  * token 0 = derive from ctrl->step, else a caller token growing by 2 per call; nblocks 0 = automatic */
 int b200_comm_run(void* plan, int mode, int opt, unsigned int token, int nblocks, void* stream);
-/* engine created on the arena's buffers ([params][grads][sq_avg][acc_delta], ParamLayout.total floats each) */
+/* engine created on the arena's buffers ([params][grads][sq_avg][acc_delta][reduced conv gradients],
+ * ParamLayout.total floats each); modes: 0 one-shot, 1 two-shot, 2 NVLS, for the fc bucket / the conv2 half */
 int b200_ddp_attach(void* engine, void* arena, int mode_bucket0, int mode_bucket1);
 
 #ifdef __cplusplus

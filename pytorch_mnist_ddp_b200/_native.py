@@ -113,23 +113,18 @@ _SIGNATURES = {
     "b200_conv1_wgrad": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp],
     "b200_reduce_partials": [_vp, _vp, _i, _i, _i, _vp],
     "b200_conv1_wgrad_noalloc": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _vp],
+    "b200_conv1_wgrad_noalloc_max_batch": [],
     "b200_conv2_fwd_simt": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _vp],
     "b200_conv2_dgrad_simt": [_vp, _vp, _vp, _vp, _vp, _i, _vp],
     "b200_conv2_wgrad_simt": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _vp],
-    "b200_unpool_dense": [_vp, _vp, _vp, _vp, _vp, _i, _vp],
     "b200_sgemm": [_vp, _l, _l, _vp, _l, _l, _vp, _i, _i, _i, _i, _i, _vp, _f, _vp],
     "b200_tc_gemm": [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp, _f, _vp],
-    "b200_fc1_dgrad_unpool_tc": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _f, _vp],
+    "b200_tc_gemm_ex": [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp, _f, _i, _vp],
     "b200_conv2_fwd_tc": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _vp],
-    "b200_conv2_fwd_tc2": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _vp],
-    "b200_conv2_dgrad_tc2": [_vp, _vp, _vp, _vp, _i, _vp],
-    "b200_conv2_fwd_tc3": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _vp],
-    "b200_conv2_dgrad_tc3": [_vp, _vp, _vp, _vp, _i, _vp],
-    "b200_conv2_dgrad_tc4": [_vp, _vp, _vp, _vp, _vp, _i, _vp],
-    "b200_conv12_fwd_tc4": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp],
-    "b200_conv2_wgrad_tc2": [_vp, _vp, _vp, _vp, _i, _vp],
-    "b200_conv2_dgrad_tc": [_vp, _vp, _vp, _vp, _i, _vp],
-    "b200_conv2_wgrad_tc": [_vp, _vp, _vp, _vp, _i, _vp],
+    "b200_conv12_fwd_tc": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp],
+    "b200_conv2_dgrad_tc": [_vp, _vp, _vp, _vp, _vp, _i, _vp],
+    "b200_conv2_wgrad_tc_parts": [_i],
+    "b200_conv2_wgrad_tc": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _vp],
     "b200_head_fused": [_vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp],
     "b200_head_wgrad": [_vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp],
     "b200_engine_host_loss_ring": [_vp, ctypes.POINTER(ctypes.POINTER(ctypes.c_float))],
@@ -150,6 +145,9 @@ _SIGNATURES = {
                                        ctypes.c_size_t, ctypes.c_size_t, _i, ctypes.POINTER(_vp),
                                        ctypes.POINTER(_vp)],
     "b200_comm_plan_destroy": [_vp],
+    "b200_comm_conv_plan_create_emulated": [ctypes.POINTER(_vp), _i, ctypes.c_size_t, ctypes.POINTER(_vp),
+                                            ctypes.POINTER(_vp)],
+    "b200_comm_conv_bucket_emulated": [_vp, _i, ctypes.POINTER(_vp), _i, ctypes.POINTER(_vp), _i, _i, _vp, _vp],
     "b200_comm_run": [_vp, _i, _i, ctypes.c_uint, _i, _vp],
     "b200_ddp_attach": [_vp, _vp, _i, _i],
     "b200_engine_create": [ctypes.POINTER(EngineConfig), ctypes.POINTER(_vp)],
@@ -190,6 +188,7 @@ def lib() -> ctypes.CDLL:
                 raise NativeError(f"libb200mnist.so is not built and cannot be built here: {e}") from e
     L = ctypes.CDLL(path)
     L.b200_last_error.restype = ctypes.c_char_p
+    L.b200_comm_fault_message.restype = ctypes.c_char_p
     L.b200_launch_count.restype = ctypes.c_longlong
     for name, sig in _SIGNATURES.items():
         fn = getattr(L, name, None)

@@ -29,13 +29,15 @@ from .utils.data import MnistSplit
  BUF_DLOGITS, BUF_DH, BUF_DP, BUF_DA1, BUF_LOSS_I, BUF_LOSS_RING, BUF_CTRL, BUF_LOGP, BUF_STAGE_IMG,
  BUF_STAGE_LBL, BUF_FC1_PART) = range(20)
 LOSS_RING = 1024
-TC_CONV2_FWD, TC_FC1_FWD, TC_FC1_BWD, TC_CONV2_BWD, TC_CONV2_V2, TC_CONV2_V3 = 1, 2, 4, 8, 16, 32
-TC_ALL = 63
-DEFAULT_TC = TC_ALL
+# B200EngineConfig.use_tc bits (csrc/engine.h): which layers run on the tcgen05 kernels; TC_FC1_FP32 makes the fc1
+# GEMMs 3xTF32 split-operand products (fp32-class, what the reference's fp32 SGEMM delivers)
+TC_CONV2_FWD, TC_FC1_FWD, TC_FC1_BWD, TC_CONV2_BWD, TC_FC1_FP32 = 1, 2, 4, 8, 16
+TC_ALL = 15              # every layer on tensor cores, fc1 in single-pass TF32
+DEFAULT_TC = TC_ALL | TC_FC1_FP32
 
 
 def default_tc_mask() -> int:
-    """Which layers run on tcgen05 tensor cores (bit mask); B200_TC=0 forces CUDA cores."""
+    """Which layers run on tcgen05 tensor cores (bit mask); B200_TC=0 forces CUDA cores, 15 = TF32 fc1."""
     env = os.environ.get("B200_TC")
     if env is not None:
         return int(env, 0)

@@ -49,14 +49,14 @@ def conv1_fwd(images_u8: torch.Tensor, idx: Optional[torch.Tensor], ctrl: torch.
     return a1
 
 
-def conv12_fwd_draft(images_u8: torch.Tensor, idx: Optional[torch.Tensor], ctrl: torch.Tensor, w1: torch.Tensor,
-                     b1: torch.Tensor, w2: torch.Tensor, b2: torch.Tensor, batch: int):
-    """DRAFT kernel (tc_conv2_v4.cu, never run on a GPU yet): conv1 + conv2 forward in one launch."""
+def conv12_fwd(images_u8: torch.Tensor, idx: Optional[torch.Tensor], ctrl: torch.Tensor, w1: torch.Tensor,
+               b1: torch.Tensor, w2: torch.Tensor, b2: torch.Tensor, batch: int):
+    """conv1 + conv2 forward in one launch (csrc/tc_conv2_fwd.cu): returns (a1, pooled, amax)."""
     a1 = torch.empty(batch, 26, 26, 32, device="cuda")
     pooled = torch.empty(batch, 12, 12, 64, device="cuda")
     amax = torch.empty(batch, 12, 12, 64, dtype=torch.uint8, device="cuda")
-    N.check(N.lib().b200_conv12_fwd_tc4(_p(images_u8), _p(idx), _p(ctrl), _p(w1), _p(b1), _p(a1), _p(w2), _p(b2),
-                                        _p(pooled), _p(amax), batch, _s()))
+    N.check(N.lib().b200_conv12_fwd_tc(_p(images_u8), _p(idx), _p(ctrl), _p(w1), _p(b1), _p(a1), _p(w2), _p(b2),
+                                       _p(pooled), _p(amax), batch, _s()))
     return a1, pooled, amax
 
 
@@ -73,72 +73,40 @@ def conv2_fwd(a1: torch.Tensor, w: torch.Tensor, b: torch.Tensor, ctrl: torch.Te
     pooled = torch.empty(batch, 12, 12, 64, device="cuda")
     amax = torch.empty(batch, 12, 12, 64, dtype=torch.uint8, device="cuda")
     L = N.lib()
-    fn = {2: L.b200_conv2_fwd_tc2, 3: L.b200_conv2_fwd_tc3}.get(tc, L.b200_conv2_fwd_tc if tc else L.b200_conv2_fwd_simt)
+    fn = L.b200_conv2_fwd_tc if tc else L.b200_conv2_fwd_simt
     N.check(fn(_p(a1), _p(w), _p(b), _p(ctrl), _p(pooled), _p(amax), batch, _s()))
     return pooled, amax
-
-
-def unpool_dense(dp: torch.Tensor, amax: torch.Tensor, with_db: bool = False):
-    batch = dp.shape[0]
-    L = N.lib()
-    dy = torch.empty(batch, 24, 24, 64, device="cuda")
-    if not with_db:
-        N.check(L.b200_unpool_dense(_p(dp), _p(amax), _p(dy), None, None, batch, _s()))
-        return dy
-    part = torch.empty(L.b200_unpool_parts() * 64, device="cuda")
-    db = torch.empty(64, device="cuda")
-    N.check(L.b200_unpool_dense(_p(dp), _p(amax), _p(dy), _p(part), _p(db), batch, _s()))
-    return dy, db
-
-
-def fc1_dgrad_unpool(dh: torch.Tensor, w1: torch.Tensor, pooled: torch.Tensor, amax: torch.Tensor, scale: float):
-    """Fused fc1 dgrad + mask + un-pool: returns (dY [B,24,24,64], conv2 bias gradient [64])."""
-    batch = dh.shape[0]
-    mt = (batch + 127) // 128
-    dy = torch.empty(batch, 24, 24, 64, device="cuda")
-    part = torch.empty(mt, 9216, device="cuda")
-    N.check(N.lib().b200_fc1_dgrad_unpool_tc(_p(dh), _p(w1), _p(pooled), _p(amax), _p(dy), _p(part), batch, scale, _s()))
-    return dy, part.view(mt * 144, 64).sum(0)
 
 
 def conv2_dgrad(dp, amax, w, a1, tc: bool = False) -> torch.Tensor:
     batch = dp.shape[0]
     da1 = torch.empty(batch, 26, 26, 32, device="cuda")
-    if tc == 4:  # draft kernel: expands (dp, amax) itself, no dense dY
-        N.check(N.lib().b200_conv2_dgrad_tc4(_p(dp), _p(amax), _p(w), _p(a1), _p(da1), batch, _s()))
-        return da1
-    if tc:
-        dy = unpool_dense(dp, amax)
-        L = N.lib()
-        fn = {2: L.b200_conv2_dgrad_tc2, 3: L.b200_conv2_dgrad_tc3}.get(tc, L.b200_conv2_dgrad_tc)
-        N.check(fn(_p(dy), _p(w), _p(a1), _p(da1), batch, _s()))
-    else:
-        N.check(N.lib().b200_conv2_dgrad_simt(_p(dp), _p(amax), _p(w), _p(a1), _p(da1), batch, _s()))
+    fn = N.lib().b200_conv2_dgrad_tc if tc else N.lib().b200_conv2_dgrad_simt
+    N.check(fn(_p(dp), _p(amax), _p(w), _p(a1), _p(da1), batch, _s()))
     return da1
 
 
 def conv2_wgrad(dp, amax, a1, tc: bool = False) -> Tuple[torch.Tensor, torch.Tensor]:
     batch = dp.shape[0]
     L = N.lib()
-    part = torch.empty(L.b200_conv2_wgrad_parts() * (18432 + 64), device="cuda")
+    parts = L.b200_conv2_wgrad_tc_parts(batch) if tc else L.b200_conv2_wgrad_parts()
+    part = torch.empty(parts * (18432 + 64), device="cuda")
     dw, db = torch.empty(9, 64, 32, device="cuda"), torch.empty(64, device="cuda")
-    if tc:
-        dy, db = unpool_dense(dp, amax, with_db=True)
-        fn = L.b200_conv2_wgrad_tc2 if tc in (2, 3) else L.b200_conv2_wgrad_tc
-        N.check(fn(_p(dy), _p(a1), _p(part), _p(dw), batch, _s()))
-    else:
-        N.check(L.b200_conv2_wgrad_simt(_p(dp), _p(amax), _p(a1), _p(part), _p(dw), _p(db), batch, _s()))
+    fn = L.b200_conv2_wgrad_tc if tc else L.b200_conv2_wgrad_simt
+    N.check(fn(_p(dp), _p(amax), _p(a1), _p(part), _p(dw), _p(db), batch, _s()))
     return dw, db
 
 
 def gemm(A: torch.Tensor, B: torch.Tensor, a_mn: bool, b_mn: bool, M: int, N_: int, K: int, splits: int = 1,
-         tc: bool = False, aux: Optional[torch.Tensor] = None, scale: float = 0.0) -> torch.Tensor:
-    """D[M][N] = A.B.  a_mn False: A is [M][K]; True: A is [K][M].  b_mn False: B is [N][K]; True: [K][N]."""
+         tc: bool = False, aux: Optional[torch.Tensor] = None, scale: float = 0.0, fp32: bool = False) -> torch.Tensor:
+    """D[M][N] = A.B.  a_mn False: A is [M][K]; True: A is [K][M].  b_mn False: B is [N][K]; True: [K][N].
+    tc: tcgen05 kernel (TF32; fp32=True: 3xTF32 split-operand product), else the fp32 CUDA-core GEMM."""
     D = torch.empty(splits, M, N_, device="cuda")
     epi = 0 if aux is None else 1
     L = N.lib()
     if tc:
-        N.check(L.b200_tc_gemm(_p(A), _p(B), _p(D), M, N_, K, int(a_mn), int(b_mn), splits, epi, _p(aux), scale, _s()))
+        N.check(L.b200_tc_gemm_ex(_p(A), _p(B), _p(D), M, N_, K, int(a_mn), int(b_mn), splits, epi, _p(aux), scale,
+                                  int(fp32), _s()))
     else:
         sam, sak = (1, M) if a_mn else (K, 1)
         sbk, sbn = (N_, 1) if b_mn else (1, K)

@@ -15,14 +15,17 @@ is rebuilt here on top of csrc/symm.cu and csrc/allreduce.cu:
   the end (SURVEY N17 bucket layout; section 8 rows 11, 12, 15).
 
 Reduction modes (``--comm``): ``oneshot`` (every rank reduces the whole bucket), ``twoshot``
-(reduce-scatter + sharded Adadelta + parameter all-gather), ``auto`` = two-shot for the 4.7 MB fc
-bucket, except at world == 2 where it is ``nvls`` when the arena gets a multicast mapping; ``nvls`` = two-shot through the NVSwitch
-(``multimem.ld_reduce`` + ``multimem.st`` on a multicast mapping from torch symmetric memory).  ``nccl`` keeps the reference's unfused structure
-(ncclAllReduce + separate Adadelta) as the in-tree baseline.
+(reduce-scatter + sharded Adadelta + parameter all-gather), ``nvls`` = two-shot through the NVSwitch
+(``multimem.ld_reduce`` + ``multimem.st`` on a multicast mapping from torch symmetric memory), ``auto`` =
+``nvls`` when such a mapping exists, ``twoshot`` otherwise.  The mode applies to the fc bucket and to the
+conv2 half of the conv bucket (reduced on the wgrad branch, under the rest of the backward pass); conv1's
+1.3 KB is exchanged one-shot by the step's last kernel.  ``nccl`` keeps the reference's unfused structure
+(ncclAllReduce + separate Adadelta) as the in-tree baseline, and is what multi-host jobs fall back to.
 """
 from __future__ import annotations
 
 import ctypes
+import os
 from typing import Dict, List, Optional
 
 import torch
@@ -44,12 +47,13 @@ class SymmetricArena:
         self.tokens: Dict[int, int] = {}
 
     @classmethod
-    def create(cls, info: DistInfo, payload_floats: int) -> "SymmetricArena":
+    def create(cls, info: DistInfo, payload_floats: int, exchange: bool = True) -> "SymmetricArena":
+        """exchange=False: a purely local arena (no IPC handles exchanged, peers unmapped) for the NCCL baseline."""
         lib = N.lib()
         h = ctypes.c_void_p()
         N.check(lib.b200_symm_create(info.world_size, info.rank, payload_floats * 4, ctypes.byref(h)))
         arena = cls(h, info.world_size, info.rank, payload_floats)
-        if info.world_size > 1:
+        if info.world_size > 1 and exchange:
             nb = lib.b200_symm_handle_bytes()
             mine = (ctypes.c_char * nb)()
             N.check(lib.b200_symm_export(h, mine))
@@ -156,61 +160,73 @@ class CommPlan:
 
 
 class FusedDataParallel:
+    """Arena layout per rank, in floats: ``[params T | grads T | sq_avg T | acc_delta T | reduced conv grads T]``."""
+
+    REGIONS = 5
+
     def __init__(self, info: DistInfo, comm: str = "auto") -> None:
         if comm not in ("auto", "oneshot", "twoshot", "nccl", "nvls"):
             raise ValueError(f"unknown comm mode {comm}")
         self.info, self.comm = info, comm
-        w = info.world_size
-        if comm == "auto":  # resolved in allocate(): two-shot, or NVLS at world == 2 when a multicast mapping exists
-            self.modes = (TWOSHOT, ONESHOT)
-        elif comm == "twoshot":
-            self.modes = (TWOSHOT, ONESHOT)
-        elif comm == "nvls":  # fc bucket through the switch (multimem), conv bucket one-shot P2P
-            self.modes = (NVLS, ONESHOT)
-        else:
-            self.modes = (ONESHOT, ONESHOT)
+        # (fc bucket, conv2 half of the conv bucket); conv1's 1.3 KB is always exchanged one-shot in the last kernel
+        self.modes = {"oneshot": (ONESHOT, ONESHOT), "twoshot": (TWOSHOT, TWOSHOT), "nvls": (NVLS, NVLS),
+                      "auto": (TWOSHOT, TWOSHOT), "nccl": (ONESHOT, ONESHOT)}[comm]
         self.mode = comm
         self.arena: Optional[SymmetricArena] = None
         self.total = 0
 
+    def _single_host(self) -> bool:
+        """CUDA IPC and multicast mappings only exist between GPUs of one host: compare host names."""
+        if not (dist.is_initialized() and self.info.world_size > 1):
+            return True
+        import socket
+        names = [None] * self.info.world_size
+        dist.all_gather_object(names, socket.gethostname())
+        return len(set(names)) == 1
+
     def allocate(self, total_floats: int) -> Dict[str, int]:
         """Create the arena and return the raw pointers the engine must use for its flat buffers."""
         self.total = total_floats
+        n = self.REGIONS * total_floats
+        if self.comm != "nccl" and not self._single_host():
+            # the reference's env contract reaches across nodes (mnist_ddp.py:16-22,134); peer-mapped memory does not
+            if self.info.rank == 0:
+                print(f"b200: ranks are on different hosts -- NVLink peer memory is unavailable, falling back from "
+                      f"--comm {self.comm} to --comm nccl (ncclAllReduce per bucket + separate Adadelta)", flush=True)
+            self.comm = self.mode = "nccl"
         if self.comm == "nvls":
-            self.arena = SymmetricArena.create_torch(self.info, 4 * total_floats)
+            self.arena = SymmetricArena.create_torch(self.info, n)
             if not getattr(self.arena, "has_multicast", False):
                 raise N.NativeError("--comm nvls: this host/driver gave no multicast mapping (NVLS unavailable)")
-        elif self.comm == "auto" and self.info.world_size != 2:
-            # world >= 4: two-shot on the CUDA-IPC arena.  NVLS was equal to two-shot at 4 and 8 GPUs with the
-            # earlier engine (168.0 vs 167.6 us/step at 8), and the current engine (branch streams, 96-CTA
-            # reducer) has only been run on real hardware at 2 GPUs: the one 8-GPU attempt with auto = NVLS
-            # was killed by the job limit before it printed anything, so that combination is unverified.
-            self.arena = SymmetricArena.create(self.info, 4 * total_floats)
-            self.mode = "auto(twoshot+oneshot)"
         elif self.comm == "auto":
-            # world == 2, measured on B200 inside one job (us/step): NVLS 142.2, two-shot 155.7; across jobs the
-            # spread is about +-5 us.  Every rank must take the same branch, so the outcome of the multicast
-            # probe is agreed on with an all-reduce.
-            arena = None
-            try:
-                arena = SymmetricArena.create_torch(self.info, 4 * total_floats)
-                ok = 1 if getattr(arena, "has_multicast", False) else 0
-            except Exception:
-                ok = 0
+            # NVLS (in-switch reduction, constant bytes per GPU) when torch symmetric memory hands out a multicast
+            # mapping, two-shot over CUDA IPC otherwise.  Every rank must take the same branch, so the outcome of
+            # the probe is agreed on with an all-reduce.
+            arena, ok = None, 0
+            if os.environ.get("B200_NO_NVLS") != "1":
+                try:
+                    arena = SymmetricArena.create_torch(self.info, n)
+                    ok = 1 if getattr(arena, "has_multicast", False) else 0
+                except Exception:
+                    ok = 0
             flag = torch.tensor([ok], device="cuda", dtype=torch.int32)
             if dist.is_initialized():
                 dist.all_reduce(flag, op=dist.ReduceOp.MIN)
             if int(flag.item()) == 1:
                 self.arena = arena
-                self.modes = (NVLS, ONESHOT)
-                self.mode = "auto(nvls+oneshot)"
+                self.modes = (NVLS, NVLS)
+                self.mode = "auto(nvls)"
             else:
                 if arena is not None:
                     arena.destroy()
-                self.arena = SymmetricArena.create(self.info, 4 * total_floats)
-                self.mode = "auto(twoshot+oneshot)"
+                self.arena = SymmetricArena.create(self.info, n)
+                self.mode = "auto(twoshot)"
         else:
-            self.arena = SymmetricArena.create(self.info, 4 * total_floats)
+            self.arena = SymmetricArena.create(self.info, n, exchange=self.comm != "nccl")
+        env = os.environ.get("B200_DDP_MODES")  # diagnostics: "fc,conv2" with 0 one-shot / 1 two-shot / 2 NVLS
+        if env:
+            self.modes = tuple(int(x) for x in env.split(","))[:2]
+            self.mode += f"[modes {self.modes[0]},{self.modes[1]}]"
         base = self.arena.base_ptr()
         t = total_floats * 4
         return {"params": base, "grads0": base + t, "grads1": base + t, "sq_avg": base + 2 * t,
@@ -222,19 +238,35 @@ class FusedDataParallel:
         barrier = dist.barrier if dist.is_initialized() else (lambda: None)
         engine.synchronize()
         barrier()
-        N.check(lib.b200_symm_pull(self.arena.handle, 0, 0, self.total, engine._s()))
+        if self.comm == "nccl":
+            if dist.is_initialized():
+                with engine.on_stream():
+                    dist.broadcast(engine.params, src=0)
+        else:
+            N.check(lib.b200_symm_pull(self.arena.handle, 0, 0, self.total, engine._s()))
         engine.synchronize()
         barrier()
         if self.comm != "nccl":
             N.check(lib.b200_ddp_attach(engine.handle, self.arena.handle, self.modes[0], self.modes[1]))
         barrier()
 
-    def verify_replicas(self) -> float:
-        """max |p_rank - p_rank0| over all parameters (should be exactly 0: fixed reduction order)."""
+    def replica_drift(self) -> float:
+        """max |p_rank - p_rank0| over all parameters, reduced over ranks.  Must be exactly 0: every element is
+        summed by one owner (two-shot / NVLS) or in a fixed rank order (one-shot), so replicas stay bit-identical.
+        Collective: every rank must call it at the same step."""
         torch.cuda.synchronize()
-        dist.barrier()
+        if dist.is_initialized():
+            dist.barrier()
         mine = self.arena.view()[: self.total]
-        ref = self.arena.view(0)[: self.total]
+        if self.comm == "nccl":
+            ref = mine.clone()
+            if dist.is_initialized():
+                dist.broadcast(ref, src=0)
+        else:
+            ref = self.arena.view(0)[: self.total]
         d = (mine - ref).abs().max()
-        dist.all_reduce(d, op=dist.ReduceOp.MAX)
+        if dist.is_initialized():
+            dist.all_reduce(d, op=dist.ReduceOp.MAX)
         return float(d.item())
+
+    verify_replicas = replica_drift

@@ -96,17 +96,82 @@ def test_fused_allreduce_adadelta_emulated(world, mode):
         a.destroy()
 
 
+CONV_BUCKET = 19456  # floats: conv2.weight 18432 | conv2.bias 256 | conv1.weight 512 | conv1.bias 256 (ParamLayout)
+
+
+@pytest.mark.parametrize("world", [1, 2, 4, 8])
+@pytest.mark.parametrize("mode", [0, 1])
+def test_conv_bucket_kernels_emulated(world, mode):
+    """conv2_reduce_kernel (partial rows -> gradient -> all-reduce into every rank's reduced buffer) followed by
+    conv_finalize_kernel (conv1 partial rows, one-shot exchange, Adadelta on the whole conv bucket, step advance):
+    W emulated ranks on one GPU against torch.optim.Adadelta on the averaged gradient."""
+    import ctypes
+    from pytorch_mnist_ddp_b200 import _native as N
+    from pytorch_mnist_ddp_b200.ops import native_ops as ops
+    from pytorch_mnist_ddp_b200.parallel.fused_ddp import SymmetricArena
+    n, np2, ng = CONV_BUCKET, 37, 13
+    arenas = SymmetricArena.create_emulated(world, 5 * n)
+    g = torch.Generator(device="cuda").manual_seed(11)
+    p0 = torch.randn(n, device="cuda", generator=g)
+    real = torch.zeros(n, dtype=torch.bool, device="cuda")  # padding floats carry no gradient and must stay put
+    real[:18432 + 64] = True; real[18688:18688 + 288] = True; real[19200:19232] = True
+    for a in arenas:
+        v = a.view()
+        v[:n] = p0
+        v[n:2 * n] = float("nan")       # gradients: every float the kernels read must have been written by them
+        v[2 * n:4 * n] = 0              # Adadelta state
+        v[4 * n:] = float("nan")        # reduced gradients
+    ctrls = [ops.make_ctrl(step=0, lr=1.0) for _ in range(world)]
+    lib = N.lib()
+    hs = (ctypes.c_void_p * world)(*[a.handle for a in arenas])
+    cs = (ctypes.c_void_p * world)(*[c.data_ptr() for c in ctrls])
+    plan = ctypes.c_void_p()
+    N.check(lib.b200_comm_conv_plan_create_emulated(hs, world, n, cs, ctypes.byref(plan)))
+    ref_p = p0.clone().requires_grad_(True)
+    opt = torch.optim.Adadelta([ref_p], lr=1.0)
+    counters = torch.zeros(8, dtype=torch.int32, device="cuda")
+    for step in range(3):
+        c2 = [torch.randn(np2, 18496, device="cuda", generator=g) * 0.01 for _ in range(world)]
+        c1 = [torch.randn(ng, 320, device="cuda", generator=g) * 0.01 for _ in range(world)]
+        torch.cuda.synchronize()
+        p2 = (ctypes.c_void_p * world)(*[t.data_ptr() for t in c2])
+        p1 = (ctypes.c_void_p * world)(*[t.data_ptr() for t in c1])
+        N.check(lib.b200_comm_conv_bucket_emulated(plan, mode, p2, np2, p1, ng, 200, counters.data_ptr(),
+                                                   torch.cuda.current_stream().cuda_stream))
+        torch.cuda.synchronize()
+        grad = torch.zeros(n, device="cuda", dtype=torch.float64)
+        for r in range(world):
+            grad[:18496] += c2[r].double().sum(0)
+            grad[18688:18688 + 288] += c1[r][:, :288].double().sum(0)
+            grad[19200:19232] += c1[r][:, 288:].double().sum(0)
+        ref_p.grad = (grad / world).float()
+        opt.step()
+        for r in range(world):
+            assert torch.equal(arenas[r].view()[:n], arenas[0].view()[:n]), f"step {step}: rank {r} drifted"
+            c = ops.read_ctrl(ctrls[r])
+            assert c["step"] == step + 1 and c["pos"] == 200 * (step + 1), c
+        got = arenas[0].view()[:n]
+        torch.testing.assert_close(got[real], ref_p.detach()[real], rtol=1e-4, atol=1e-5)
+        assert torch.equal(got[~real], p0[~real])
+    N.check(lib.b200_comm_plan_destroy(plan))
+    for a in arenas:
+        a.destroy()
+
+
 def _torchrun(nproc, script_args, timeout=600):
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}",
            "--master-addr", "127.0.0.1", "--master-port", "29533"] + script_args
     return subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=timeout)
 
 
-@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs >= 2 GPUs")
+@pytest.mark.parametrize("world", [2, 4, 8])
 @pytest.mark.parametrize("comm", ["oneshot", "twoshot", "nvls", "auto"])
-def test_multi_gpu_ddp_equivalence(comm):
-    """2 ranks x batch b without dropout == 1 rank x batch 2b ('DDP equivalence')."""
-    res = _torchrun(2, ["tests/ddp_worker.py", "--comm", comm])
+def test_multi_gpu_ddp_equivalence(comm, world):
+    """W ranks x batch b without dropout == 1 rank x batch W*b ('DDP equivalence'), replicas
+    bit-identical, CUDA-graph replay with the communication kernels captured inside."""
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs >= {world} GPUs")
+    res = _torchrun(world, ["tests/ddp_worker.py", "--comm", comm])
     if comm == "nvls" and "NVLS unavailable" in res.stdout + res.stderr:
         pytest.skip("no multicast mapping on this host")
     assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]

@@ -24,7 +24,7 @@ def _data(n_train=1024, n_test=512):
     return synthetic_split(True, n_train), synthetic_split(False, n_test)
 
 
-def _engine(train, test, max_batch=256, use_tc=0, seed=1):
+def _engine(train, test, max_batch=256, use_tc=0, seed=1):  # use_tc=None: the default mask
     from pytorch_mnist_ddp_b200.engine import NativeEngine
     from pytorch_mnist_ddp_b200.models.net import Net
     torch.manual_seed(seed)
@@ -42,22 +42,27 @@ def _norm(u8):
 
 def _tc_masks():
     from pytorch_mnist_ddp_b200 import _native as N
-    return [0, 15, 31, 63] if N.lib().b200_has_tc() else [0]
+    return [0, 6, 9, 15, 22, 31] if N.lib().b200_has_tc() else [0]
 
 
-@pytest.mark.parametrize("use_tc", [0, 15, 31, 63] + ([127, 255] if __import__("os").environ.get("B200_DRAFT") == "1" else []))  # 64 / 128 = draft kernels of tc_conv2_v4.cu
+# 0: fp32 CUDA-core kernels everywhere; 6 / 22: fc1 on tensor cores only (TF32 / 3xTF32 = fp32-class); 9: conv2 only;
+# 15: everything TF32; 31: the default (conv2 TF32 like the reference's cuDNN convs, fc1 fp32-class like its SGEMM)
+@pytest.mark.parametrize("use_tc", [0, 6, 9, 15, 22, 31])
 @pytest.mark.parametrize("batch", [64, 200])
 def test_train_step_matches_torch_without_dropout(use_tc, batch):
     if use_tc not in _tc_masks():
         pytest.skip("tensor-core kernels not built")
     train, test = _data()
     eng, net = _engine(train, test, use_tc=use_tc)
+    tf32 = bool(use_tc & 9) or (bool(use_tc & 6) and not use_tc & 16)  # any layer in single-pass TF32?
     eng.set_dropout(False)
     net.eval()  # dropout off, gradients still flow
     opt = torch.optim.Adadelta(net.parameters(), lr=1.0)
     idx = torch.randperm(len(train))[: 3 * batch].to(torch.int32)
     eng.begin_epoch(idx)
-    tol_g = dict(rtol=5e-2, atol=2e-3) if use_tc else dict(rtol=2e-3, atol=2e-5)
+    # conv2 in TF32 flips a few near-tie max-pool winners against the fp32 oracle, which re-routes whole gradient
+    # elements: conv-path gradients are only comparable norm-wise and loosely (observed: conv1.weight 2e-2)
+    tol_g = 5e-2 if use_tc & 9 else 1e-2 if tf32 else 2e-3
     for step in range(3):
         sel = idx[step * batch: (step + 1) * batch].long()
         x, y = _norm(train.images[sel]).cuda(), train.labels[sel].long().cuda()
@@ -68,7 +73,7 @@ def test_train_step_matches_torch_without_dropout(use_tc, batch):
         got = eng.read_loss(s)
         # TF32 rounding differences are amplified by Adadelta's sign-like first updates, so the
         # tensor-core trajectory is only compared loosely after step 0
-        lim = (5e-3 if step == 0 else 2e-2 * max(1.0, loss.item())) if use_tc else 2e-4
+        lim = (5e-3 if step == 0 else 2e-2 * max(1.0, loss.item())) if tf32 else 2e-4
         assert abs(got - loss.item()) < lim, (step, got, loss.item())
         if step == 0:
             grads = eng.grad_dict()
@@ -76,15 +81,51 @@ def test_train_step_matches_torch_without_dropout(use_tc, batch):
                 g = grads[name].cuda()
                 # norm-wise: near-ties in the 2x2 max-pool may route a few gradients differently
                 rel = (g - p.grad).norm().item() / max(p.grad.norm().item(), 1e-12)
-                assert rel < tol_g["rtol"], f"{name}: relative gradient error {rel}"
+                print(f"mask {use_tc} batch {batch}: {name} relative gradient error {rel:.2e}")
+                assert rel < tol_g, f"{name}: relative gradient error {rel}"
         before = {n: p.detach().clone() for n, p in net.named_parameters()}
         opt.step()
-        if not use_tc:
+        # updated parameters, every path: Adadelta's first steps are sign-like (|delta| ~ 3e-3 wherever |g| >> 3e-3), so
+        # TF32 rounding only moves the elements whose gradient is close to zero
+        if step == 0 or not tf32:
             sd = eng.state_dict()
             for name, p in net.named_parameters():
                 upd = (p.detach() - before[name]).norm().item()
                 err = (sd[name].cuda() - p.detach()).norm().item()
-                assert err < 2e-2 * upd + 1e-6, f"{name} after step {step}: update {upd}, error {err}"
+                print(f"mask {use_tc} batch {batch} step {step}: {name} update {upd:.3e} error {err:.3e}")
+                assert err < (1e-1 if tf32 else 2e-2) * upd + 1e-6, f"{name} after step {step}: update {upd}, error {err}"
+    eng.close()
+
+
+def test_large_and_ragged_batches_default_path():
+    """The batch-4096 configuration (BASELINE config 4): full batch, its ragged last batches (3404 at 8 GPUs, 2656 at
+    1), a tiny tail; default kernels, one graph per batch size, loss against torch."""
+    from pytorch_mnist_ddp_b200.utils.data import synthetic_split
+    train, test = synthetic_split(True, 20000), synthetic_split(False, 256)
+    eng, net = _engine(train, test, max_batch=4096, use_tc=None)
+    eng.set_dropout(False)
+    net.eval()
+    opt = torch.optim.Adadelta(net.parameters(), lr=1.0)
+    sizes = [4096, 4096, 3404, 100, 4096, 2656, 100]
+    idx = torch.randperm(len(train))[: sum(sizes)].to(torch.int32)
+    eng.begin_epoch(idx)
+    o = 0
+    for step, b in enumerate(sizes):
+        sel = idx[o: o + b].long()
+        o += b
+        x, y = _norm(train.images[sel]).cuda(), train.labels[sel].long().cuda()
+        opt.zero_grad()
+        loss = F.nll_loss(net(x), y)
+        loss.backward()
+        opt.step()
+        s = eng.train_step(b)  # eager the first time a batch size is seen, then graph capture + replay
+        got = eng.read_loss(s)
+        print(f"batch {b}: loss {got:.5f} vs torch {loss.item():.5f}")
+        assert abs(got - loss.item()) < (5e-3 if step == 0 else 3e-2), (step, b, got, loss.item())
+    sd = eng.state_dict()
+    for name, p in net.named_parameters():
+        rel = (sd[name].cuda() - p.detach()).norm().item() / p.detach().norm().item()
+        assert rel < 2e-2, (name, rel)
     eng.close()
 
 

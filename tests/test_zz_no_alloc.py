@@ -59,12 +59,15 @@ def test_noalloc_conv1_wgrad_matches_regular_entry_point_twice_in_a_row():
         assert rc == 0, lib.b200_last_error().decode()
         dw, db = torch.full((9, 32), float("nan"), device="cuda"), torch.full((32,), float("nan"), device="cuda")
         torch.cuda.synchronize()
-        allocated_before = torch.cuda.memory_allocated()
+        # the driver's own count of free device memory: unlike torch's allocator statistics it would also show a
+        # cudaMalloc made inside the library
+        free_before, _ = torch.cuda.mem_get_info()
         rc = lib.b200_conv1_wgrad_noalloc(images.data_ptr(), idx.data_ptr(), ctrl.data_ptr(), da1.data_ptr(),
                                           dw.data_ptr(), db.data_ptr(), batch, stream)
         assert rc == 0, lib.b200_last_error().decode()
         torch.cuda.synchronize()
-        assert torch.cuda.memory_allocated() == allocated_before
+        free_after, _ = torch.cuda.mem_get_info()
+        assert free_after == free_before, (free_before, free_after)
         scale = dw_ref.abs().max().item()
         torch.testing.assert_close(dw, dw_ref, rtol=1e-3, atol=1e-4 * scale, msg=lambda m: f"call {call}: {m}")
         torch.testing.assert_close(db, db_ref, rtol=1e-3, atol=1e-4 * scale, msg=lambda m: f"call {call}: {m}")
@@ -82,3 +85,17 @@ def test_noalloc_conv1_wgrad_rejects_batches_beyond_its_scratch():
     msg = lib.b200_last_error().decode()
     assert "exceeds" in msg and str(limit) in msg, msg
     torch.cuda.synchronize()  # nothing was launched, the device is still healthy
+
+
+def test_noalloc_conv1_wgrad_rejects_null_pointers():
+    lib = _lib()
+    stream = torch.cuda.current_stream().cuda_stream
+    d = torch.zeros(64, device="cuda")
+    ok = [d.data_ptr()] * 6  # images, idx, ctrl, da1, dw, db
+    for missing in (0, 2, 3, 4, 5):  # idx (position 1) may be NULL: sequential addressing
+        args = list(ok)
+        args[missing] = None
+        rc = lib.b200_conv1_wgrad_noalloc(*args, 8, stream)
+        assert rc != 0, f"NULL argument {missing} was accepted"
+        assert "non-NULL" in lib.b200_last_error().decode()
+    torch.cuda.synchronize()  # nothing was launched
