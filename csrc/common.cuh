@@ -178,18 +178,31 @@ __host__ __device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint2 k) {
   return c;
 }
 
-// 4 random words for elements [4*e4, 4*e4+4) of dropout layer `layer` at optimizer step `step`.
-__host__ __device__ __forceinline__ uint4 dropout_bits4(unsigned long long seed, unsigned long long step,
-                                                        uint32_t layer, uint32_t e4) {
-  uint4 ctr = make_uint4(e4, layer, (uint32_t)step, (uint32_t)(step >> 32));
+// Dropout masks are a pure function of (seed, optimizer step, layer, element index), so any kernel -- CUDA-core or
+// tensor-core, forward or a test -- regenerates the same mask without storing it.  One Philox call yields 128 bits
+// for a BLOCK of consecutive elements:
+//   layer 1 (p = .25): 64 elements per block, 2 bits each, keep iff the two bits are not both zero  (P = 3/4 exactly)
+//   layer 2 (p = .5) : 128 elements per block, 1 bit each, keep iff the bit is set
+// A pooled pixel has 64 channels and a sample 128 hidden units, so a block is exactly one pixel / one sample: the
+// warp that owns it needs ONE Philox evaluation (the 10-round Philox was a third of the conv2 epilogue's
+// instructions when every 4 elements had their own call).
+__host__ __device__ __forceinline__ uint4 dropout_block(unsigned long long seed, unsigned long long step,
+                                                        uint32_t layer, uint32_t block) {
+  uint4 ctr = make_uint4(block, layer, (uint32_t)step, (uint32_t)(step >> 32));
   uint2 key = make_uint2((uint32_t)seed, (uint32_t)(seed >> 32));
   return philox4x32_10(ctr, key);
 }
-
-// keep with probability 1-p: threshold = p * 2^32
-__host__ __device__ __forceinline__ bool dropout_keep(uint32_t bits, uint32_t thresh) { return bits >= thresh; }
-constexpr uint32_t DROP1_THRESH = 0x40000000u;  // p = .25
-constexpr uint32_t DROP2_THRESH = 0x80000000u;  // p = .5
+__host__ __device__ __forceinline__ uint32_t block_word(const uint4& r, uint32_t w) {
+  return w == 0 ? r.x : w == 1 ? r.y : w == 2 ? r.z : r.w;
+}
+// layer 1: keep flag of element `i` (0..63) of its block
+__host__ __device__ __forceinline__ bool dropout1_keep(const uint4& r, uint32_t i) {
+  return ((block_word(r, i >> 4) >> (2 * (i & 15))) & 3u) != 0u;
+}
+// layer 2: keep flag of element `i` (0..127) of its block
+__host__ __device__ __forceinline__ bool dropout2_keep(const uint4& r, uint32_t i) {
+  return ((block_word(r, i >> 5) >> (i & 31)) & 1u) != 0u;
+}
 
 // ---- small device utilities -----------------------------------------------------------------
 __device__ __forceinline__ float warp_sum(float v) {

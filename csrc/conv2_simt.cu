@@ -82,9 +82,8 @@ conv2_fwd_simt_kernel(const float* __restrict__ a1, const float* __restrict__ w,
       const int ph = (ty >> 1) + g, pw = (tx >> 1) + wdw;
       const uint32_t e = ((uint32_t)(b * HP + ph) * WP + pw) * C2 + o;
       if (train & 2) {
-        const uint4 r = dropout_bits4(seed, step, 1u, e >> 2);
-        const uint32_t bits = (e & 3) == 0 ? r.x : (e & 3) == 1 ? r.y : (e & 3) == 2 ? r.z : r.w;
-        m = dropout_keep(bits, DROP1_THRESH) ? m * (1.0f / (1.0f - P_DROP1)) : 0.f;
+        const uint4 r = dropout_block(seed, step, 1u, e >> 6);
+        m = dropout1_keep(r, e & 63u) ? m * (1.0f / (1.0f - P_DROP1)) : 0.f;
       }
       pooled[e] = m;
       amax[e] = (uint8_t)am;

@@ -413,6 +413,10 @@ extern "C" int b200_engine_destroy(void* engine) {
     for (int i = 0; i < 2; ++i) { cudaEventDestroy(E->ev_copied[i]); cudaEventDestroy(E->ev_consumed[i]); }
   }
   for (void* p : E->owned) cudaFree(p);
+  for (int i = 0; i < 2; ++i) {
+    if (E->pin_img[i]) cudaFreeHost(E->pin_img[i]);
+    if (E->pin_lbl[i]) cudaFreeHost(E->pin_lbl[i]);
+  }
   if (E->h_scratch) cudaFreeHost(E->h_scratch);
   if (E->loss_ring_host) cudaFreeHost(E->loss_ring_host);
   delete E;
@@ -548,6 +552,34 @@ extern "C" int b200_engine_train_step_host(void* engine, const uint8_t* images_h
   E->consumed_valid[par] = true;
   E->steps++;
   return B200_OK;
+}
+
+// The data-loader path in one call: gather `batch` samples of a HOST-resident uint8 dataset by index into pinned
+// staging memory (what the reference's DataLoader worker + collate + pin thread do, mnist_ddp.py:144-168), copy
+// them to the device on the copy stream, run the step.  Replaces per-sample PIL/ToTensor/Normalize work with a
+// 784-byte memcpy per sample; normalisation happens inside the forward kernel.  The host blocks only if the pinned
+// slot of two steps ago has not been copied out yet.
+extern "C" int b200_engine_train_step_gather(void* engine, const uint8_t* images_host, const uint8_t* labels_host,
+                                             const int32_t* idx_host, int batch, int use_graph, void* stream) {
+  Engine* E = (Engine*)engine;
+  B200_REQUIRE(E && images_host && labels_host && idx_host && batch > 0 && batch <= E->cfg.max_batch,
+               "engine_train_step_gather: bad arguments (batch %d, max %d)", batch, E ? E->cfg.max_batch : 0);
+  const int par = (int)(E->steps & 1);
+  if (!E->pin_img[0]) {
+    for (int i = 0; i < 2; ++i) {
+      B200_CHECK(cudaHostAlloc((void**)&E->pin_img[i], (size_t)E->cfg.max_batch * 784, cudaHostAllocDefault));
+      B200_CHECK(cudaHostAlloc((void**)&E->pin_lbl[i], (size_t)E->cfg.max_batch, cudaHostAllocDefault));
+    }
+  }
+  if (E->copy_stream && E->consumed_valid[par]) B200_CHECK(cudaEventSynchronize(E->ev_copied[par]));
+  uint8_t* pi = E->pin_img[par];
+  uint8_t* pl = E->pin_lbl[par];
+  for (int b = 0; b < batch; ++b) {
+    const size_t src = (size_t)idx_host[b];
+    memcpy(pi + (size_t)b * 784, images_host + src * 784, 784);
+    pl[b] = labels_host[src];
+  }
+  return b200_engine_train_step_host(engine, pi, pl, batch, use_graph, stream);
 }
 
 extern "C" int b200_engine_eval_reset(void* engine, void* stream) {

@@ -81,6 +81,7 @@ struct Engine {
   bool idx_seq = true;
   int epoch_n = 0;
   uint8_t *stage_img = nullptr, *stage_lbl = nullptr;
+  uint8_t *pin_img[2] = {nullptr, nullptr}, *pin_lbl[2] = {nullptr, nullptr};  // pinned host staging (train_step_gather)
   float *a1 = nullptr, *da1 = nullptr, *pooled = nullptr, *dp = nullptr, *h = nullptr, *dh = nullptr,
         *dlogits = nullptr, *loss_i = nullptr, *logp = nullptr, *fc1_part = nullptr, *c1_part = nullptr,
         *c2_part = nullptr, *loss_ring = nullptr, *loss_scalar = nullptr;

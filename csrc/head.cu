@@ -59,11 +59,12 @@ head_fused_kernel(const float* __restrict__ part, int splits, int batch,      //
   }
   float hv[4] = {fmaxf(z.x, 0.f), fmaxf(z.y, 0.f), fmaxf(z.z, 0.f), fmaxf(z.w, 0.f)};
   if (train & 2) {
-    const uint4 r = dropout_bits4(ctrl->seed, ctrl->step, 2u, (uint32_t)(b * (FC1_OUT / 4) + lane));
-    hv[0] = dropout_keep(r.x, DROP2_THRESH) ? hv[0] * 2.f : 0.f;
-    hv[1] = dropout_keep(r.y, DROP2_THRESH) ? hv[1] * 2.f : 0.f;
-    hv[2] = dropout_keep(r.z, DROP2_THRESH) ? hv[2] * 2.f : 0.f;
-    hv[3] = dropout_keep(r.w, DROP2_THRESH) ? hv[3] * 2.f : 0.f;
+    const uint4 r = dropout_block(ctrl->seed, ctrl->step, 2u, (uint32_t)b);  // one block = this sample's 128 units
+    const uint32_t m4 = (block_word(r, lane >> 3) >> (4 * (lane & 7))) & 0xfu;  // units 4*lane .. 4*lane+3
+    hv[0] = (m4 & 1u) ? hv[0] * 2.f : 0.f;
+    hv[1] = (m4 & 2u) ? hv[1] * 2.f : 0.f;
+    hv[2] = (m4 & 4u) ? hv[2] * 2.f : 0.f;
+    hv[3] = (m4 & 8u) ? hv[3] * 2.f : 0.f;
   }
   *reinterpret_cast<float4*>(h + (size_t)b * FC1_OUT + lane * 4) = make_float4(hv[0], hv[1], hv[2], hv[3]);
 

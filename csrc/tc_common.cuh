@@ -115,6 +115,30 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16]) {
   for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
 }
 
+// the same loads without the wait, so that several can be in flight; call tmem_ld_wait() before using any result
+template <int N>
+__device__ __forceinline__ void tmem_ld_nowait(uint32_t taddr, float (&v)[N]) {
+  static_assert(N == 16 || N == 32, "tmem_ld_nowait: 16 or 32 columns");
+  uint32_t* r = reinterpret_cast<uint32_t*>(&v[0]);
+  if constexpr (N == 32) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+          "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+          "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr) : "memory");
+  } else {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr) : "memory");
+  }
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
 // ---- descriptors --------------------------------------------------------------------------------
 // shared-memory matrix descriptor (sm_100 version bit set); layout: 2 = SWIZZLE_128B,
 // 1 = SWIZZLE_128B_BASE32B (cute/arch/mma_sm100_desc.hpp UMMA::LayoutType)
@@ -168,6 +192,25 @@ __device__ __forceinline__ bool elect_one() {
 }
 
 }  // namespace tc
+
+// ---- in-kernel timeline (debug builds only: nvcc -DB200_STAMPS, see scripts/kernel_timeline.py) -----------------
+// A persistent kernel's time is made of waits between its warp roles; ncu's stall samples say which instruction
+// waits, not when.  With B200_STAMPS every role writes %globaltimer values of its milestones into a per-file device
+// array [CTA][slot]; b200_debug_stamps_<file>() copies it out.  Compiled out of the production library.
+#ifdef B200_STAMPS
+#define B200_STAMP_ARRAY(name) static __device__ unsigned long long name[160][48]
+#define B200_STAMP(name, slot)                                                             \
+  do {                                                                                     \
+    if ((threadIdx.x & 31) == 0 && (slot) < 48) {                                          \
+      unsigned long long _t;                                                               \
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(_t));                               \
+      name[blockIdx.x < 160 ? blockIdx.x : 159][(slot)] = _t;                              \
+    }                                                                                      \
+  } while (0)
+#else
+#define B200_STAMP_ARRAY(name)
+#define B200_STAMP(name, slot) do {} while (0)
+#endif
 
 // ---- host side: tensor-map creation through the driver entry point (no -lcuda needed) ----------
 namespace tcmap {

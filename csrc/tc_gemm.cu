@@ -12,12 +12,14 @@
 //
 // SPLIT = true is the fp32-class variant ("3xTF32"): the reference runs fc1 as an fp32 SGEMM
 // (torch.backends.cuda.matmul.allow_tf32 = False), and a single TF32 pass keeps only 10 mantissa
-// bits of each operand.  Every operand x is split into hi = x with its 13 low mantissa bits cleared (exactly
-// representable in TF32) and lo = x - hi (exact in fp32, |lo| < 2^-10 |x|), and the product is accumulated as
-// hi*hi + hi*lo + lo*hi into the same TMEM accumulator; the dropped terms are O(2^-20) relative.  The split is
-// done on chip: while the mainloop runs, the (otherwise idle) epilogue warps read each TMA-written stage,
-// overwrite it with hi and write lo to a second tile at the same swizzled offsets, then hand the stage to the
-// MMA warp (fence.proxy.async + mbarrier).  Nothing extra is read from or written to global memory.
+// bits of each operand.  Every operand x is split into hi = x with its 13 low mantissa bits cleared (what the
+// tensor core reads anyway: it truncates) and lo = x - hi (exact in fp32, |lo| < 2^-10 |x|), and the product is
+// accumulated as hi*hi + hi*lo + lo*hi into the same TMEM accumulator; the dropped terms are O(2^-20) relative.
+// The split is done on chip: while the mainloop runs, the (otherwise idle) epilogue warps read each TMA-written
+// stage and write lo to a second tile at the same swizzled offsets, then hand the stage to the MMA warp
+// (fence.proxy.async + mbarrier).  Nothing extra is read from or written to global memory.  What remains is the
+// tensor core's own accumulator, which truncates when it adds: on long K chains (thousands of accumulating MMAs
+// into one output) that error reaches a few 1e-5 relative; the engine keeps chains short (split-K, K = 128, K = batch).
 #include <map>
 #include <mutex>
 #include <tuple>
@@ -72,14 +74,14 @@ namespace {
 
 constexpr int BM = 128, BK = 32;
 constexpr int A_BYTES = BM * BK * 4;  // 16 KiB
-__host__ __device__ constexpr int stages_for(bool split) { return split ? 3 : 4; }
+__host__ __device__ constexpr int stages_for(bool split, int bn) { return split && bn > 64 ? 3 : 4; }  // <= 193 KiB
 
 template <int BN, bool A_MN, bool B_MN, int EPI, bool SPLIT>
 __global__ void __launch_bounds__(320, 1)
 tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
                float* __restrict__ D, int M, int N, int nkb_total, int kb_per_split, const float* __restrict__ aux,
                float scale) {
-  constexpr int STAGES = stages_for(SPLIT);
+  constexpr int STAGES = stages_for(SPLIT, BN);
   constexpr int B_BYTES = BN * BK * 4;
   constexpr int HI_BYTES = A_BYTES + B_BYTES;                 // what TMA writes per stage
   constexpr int STAGE_BYTES = SPLIT ? 2 * HI_BYTES : HI_BYTES;  // SPLIT: [A hi | B hi | A lo | B lo]
@@ -178,7 +180,9 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
     };
     if (EPI == 1) load_aux(h * 32);
     if (SPLIT) {
-      // operand split, stage by stage, by all epilogue threads: hi = x & ~0x1fff (in place), lo = x - hi
+      // operand split, stage by stage, by all epilogue threads: lo = x - (x & ~0x1fff).  The hi tile is the raw tile:
+      // kind::tf32 reads an fp32 operand by TRUNCATING it to TF32 (measured, tests/test_gpu_kernels.py:
+      // test_tf32_operand_rounding_probe), so the tensor core itself sees x & ~0x1fff there.
       const int et = (warp - 2) * 32 + lane, nthr = (nwarps - 2) * 32;
       for (int kb = 0; kb < nkb; ++kb) {
         const int s = kb % STAGES;
@@ -190,7 +194,6 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
           const uint4 hi = make_uint4(x.x & 0xffffe000u, x.y & 0xffffe000u, x.z & 0xffffe000u, x.w & 0xffffe000u);
           const float4 lo = make_float4(__uint_as_float(x.x) - __uint_as_float(hi.x), __uint_as_float(x.y) - __uint_as_float(hi.y),
                                         __uint_as_float(x.z) - __uint_as_float(hi.z), __uint_as_float(x.w) - __uint_as_float(hi.w));
-          *reinterpret_cast<uint4*>(st + o) = hi;
           *reinterpret_cast<float4*>(st + HI_BYTES + o) = lo;
         }
         fence_proxy_async();  // generic-proxy stores -> visible to the tensor core's operand reads
@@ -268,7 +271,7 @@ int get_map(const float* p, int R, int K, int mn, int tile, CUtensorMap* out) {
 template <int BN, bool A_MN, bool B_MN, int EPI, bool SPLIT>
 int launch(const CUtensorMap& ma, const CUtensorMap& mb, float* D, int M, int N, int nkb, int kbs, int splits,
            const float* aux, float scale, cudaStream_t s) {
-  constexpr int smem = stages_for(SPLIT) * (SPLIT ? 2 : 1) * (A_BYTES + BN * BK * 4) + 1024;
+  constexpr int smem = stages_for(SPLIT, BN) * (SPLIT ? 2 : 1) * (A_BYTES + BN * BK * 4) + 1024;
   static bool attr = false;
   if (!attr) {
     B200_CHECK(cudaFuncSetAttribute(tc_gemm_kernel<BN, A_MN, B_MN, EPI, SPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));

@@ -29,7 +29,7 @@ STAMP = os.path.join(LIBDIR, "libb200mnist.stamp")
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
     "-Xcompiler", "-fPIC", "-I", INCLUDE,  # no --use_fast_math: fp32 parity with the reference
-]
+] + os.environ.get("B200_EXTRA_NVCC_FLAGS", "").split()  # e.g. -DB200_STAMPS (in-kernel timelines, debug only)
 
 
 def _nvcc() -> str:
@@ -161,6 +161,7 @@ _SIGNATURES = {
     "b200_engine_apply_update": [_vp, _i, _vp],
     "b200_engine_train_step": [_vp, _i, _i, _vp],
     "b200_engine_train_step_host": [_vp, _vp, _vp, _i, _i, _vp],
+    "b200_engine_train_step_gather": [_vp, _vp, _vp, _vp, _i, _i, _vp],
     "b200_engine_eval_batch": [_vp, _i, _i, _i, _vp],
     "b200_engine_eval_reset": [_vp, _vp],
     "b200_engine_eval_result": [_vp, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_longlong), _vp],

@@ -173,6 +173,17 @@ class NativeEngine:
         self.steps += 1
         return self.steps - 1
 
+    def train_step_gather(self, images_u8: torch.Tensor, labels_u8: torch.Tensor, idx_i32: torch.Tensor,
+                          use_graph: bool = True) -> int:
+        """The data-loader path: `idx_i32` (host int32) selects this step's samples from a HOST-resident uint8
+        dataset; they are gathered into pinned staging memory by the native library, copied to the GPU on the copy
+        stream (overlapping the previous step) and trained on."""
+        N.check(self.lib.b200_engine_train_step_gather(self.handle, images_u8.data_ptr(), labels_u8.data_ptr(),
+                                                       idx_i32.data_ptr(), int(idx_i32.numel()), int(use_graph),
+                                                       self._s()))
+        self.steps += 1
+        return self.steps - 1
+
     def read_loss(self, step: int) -> float:
         out = ctypes.c_float()
         N.check(self.lib.b200_engine_read_loss(self.handle, step, ctypes.byref(out), self._s()))
@@ -265,6 +276,13 @@ class B200Backend:
     def step_host(self, images_u8: torch.Tensor, labels_u8: torch.Tensor) -> int:
         """Same as `step`, but the batch is streamed from pinned host memory (uint8 images, uint8 labels)."""
         s = self.engine.train_step_host(images_u8, labels_u8, self.use_graph)
+        if self._nccl_baseline:
+            self._nccl_reduce_and_update(0)
+        return s
+
+    def step_gather(self, images_u8: torch.Tensor, labels_u8: torch.Tensor, idx_i32: torch.Tensor) -> int:
+        """Same as `step_host`, with the batch gathered by index from a host-resident uint8 dataset."""
+        s = self.engine.train_step_gather(images_u8, labels_u8, idx_i32, self.use_graph)
         if self._nccl_baseline:
             self._nccl_reduce_and_update(0)
         return s
