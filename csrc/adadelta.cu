@@ -47,41 +47,41 @@ adadelta_kernel(float* __restrict__ p, const float* __restrict__ g, float* __res
 
 // conv2's half of the conv bucket on one GPU: reduce the wgrad kernel's per-CTA partial rows into the
 // gradient buffer.  Runs on the wgrad branch, under conv2 dgrad / conv1 wgrad (11 MB of partials at 148
-// CTAs would otherwise be read by the step's last kernel).  One CTA per 256-float chunk.
-__global__ void __launch_bounds__(64 * FIN_SLICES)
+// CTAs would otherwise be read by the step's last kernel).  One CTA per FIN_CHUNK-float chunk.
+__global__ void __launch_bounds__(FIN_THREADS)
 reduce_segs_kernel(float* __restrict__ dst, FinalizeSegs segs) {
-  __shared__ float4 red[FIN_SLICES][64];
+  __shared__ float4 red[FIN_SLICES][FIN_COLS];
   pdl_trigger();
   pdl_wait();
-  const int off = blockIdx.x * 256;
+  const int off = blockIdx.x * FIN_CHUNK;
   const float4 t = reduce_partial_chunk(segs, off, red);
-  if (threadIdx.x < 64) *reinterpret_cast<float4*>(dst + off + 4 * threadIdx.x) = t;
+  if (threadIdx.x < FIN_COLS) *reinterpret_cast<float4*>(dst + off + 4 * threadIdx.x) = t;
 }
 
-// Single-GPU end-of-step kernel.  CTAs [0, nchunks) each own 256 floats of the conv bucket: chunks below
+// Single-GPU end-of-step kernel.  CTAs [0, nchunks) each own FIN_CHUNK floats of the conv bucket: chunks below
 // first_partial already have their gradient in g (conv2, reduced on the wgrad branch), the others (conv1)
 // reduce their partial rows in a fixed order first; then Adadelta.  The remaining CTAs stream over the fc
 // bucket unless that was updated on the fc branch already.  The last CTA to finish advances the step.
-__global__ void __launch_bounds__(64 * FIN_SLICES)
+__global__ void __launch_bounds__(FIN_THREADS)
 adadelta_finalize_kernel(float* __restrict__ p, float* __restrict__ g, float* __restrict__ v, float* __restrict__ u,
                          int b0_n4, int b1_off, int nchunks, int first_partial, FinalizeSegs segs,
                          B200Ctrl* __restrict__ ctrl, float rho, float eps, int advance,
                          unsigned int* __restrict__ done_counter) {
-  __shared__ float4 red[FIN_SLICES][64];
+  __shared__ float4 red[FIN_SLICES][FIN_COLS];
   pdl_trigger();
   pdl_wait();
   const float lr = ctrl->lr;
   if ((int)blockIdx.x < nchunks) {
-    const int col = threadIdx.x & 63, off = blockIdx.x * 256;
+    const int col = threadIdx.x % FIN_COLS, off = blockIdx.x * FIN_CHUNK;
     const size_t i = (size_t)b1_off + off + 4 * col;
     float4 t;
     if ((int)blockIdx.x >= first_partial) {
       t = reduce_partial_chunk(segs, off, red);
-      if (threadIdx.x < 64) *reinterpret_cast<float4*>(g + i) = t;  // keep the gradient buffer complete (tests, debugging)
-    } else if (threadIdx.x < 64) {
+      if (threadIdx.x < FIN_COLS) *reinterpret_cast<float4*>(g + i) = t;  // keep the gradient buffer complete (tests, debugging)
+    } else if (threadIdx.x < FIN_COLS) {
       t = *reinterpret_cast<const float4*>(g + i);
     }
-    if (threadIdx.x < 64) {
+    if (threadIdx.x < FIN_COLS) {
       float4 pp = *reinterpret_cast<float4*>(p + i), vv = *reinterpret_cast<float4*>(v + i),
              uu = *reinterpret_cast<float4*>(u + i);
       adadelta_update(t.x, pp.x, vv.x, uu.x, lr, rho, eps);
@@ -122,13 +122,13 @@ adadelta_finalize_kernel(float* __restrict__ p, float* __restrict__ g, float* __
 
 int b200_reduce_segs(float* dst, int nchunks, const FinalizeSegs& segs, cudaStream_t s) {
   B200_REQUIRE(dst && nchunks > 0, "reduce_segs: bad arguments");
-  B200_CHECK(b200_launch(reduce_segs_kernel, dim3(nchunks), dim3(64 * FIN_SLICES), 0, s, dst, segs));
+  B200_CHECK(b200_launch(reduce_segs_kernel, dim3(nchunks), dim3(FIN_THREADS), 0, s, dst, segs));
   b200_count_launch();
   B200_LAUNCH_CHECK();
   return B200_OK;
 }
 
-// bucket 0 = floats [0, b1_off) (fc), bucket 1 = floats [b1_off, b1_off + 256*nchunks) (conv)
+// bucket 0 = floats [0, b1_off) (fc), bucket 1 = floats [b1_off, b1_off + FIN_CHUNK*nchunks) (conv)
 int b200_adadelta_finalize(float* p, float* g, float* v, float* u, long b1_off, int nchunks, int first_partial,
                            const FinalizeSegs& segs, void* ctrl, float rho, float eps, int advance,
                            unsigned int* done_counter, bool bucket0_done, cudaStream_t s) {
@@ -136,7 +136,7 @@ int b200_adadelta_finalize(float* p, float* g, float* v, float* u, long b1_off, 
                "adadelta_finalize: bad bucket layout");
   // bucket0_done: the fc bucket was already updated elsewhere (engine branch stream); only the conv chunks run
   const int grid = nchunks + (bucket0_done ? 0 : 2 * b200_sm_count());
-  B200_CHECK(b200_launch(adadelta_finalize_kernel, dim3(grid), dim3(64 * FIN_SLICES), 0, s, p, g, v, u,
+  B200_CHECK(b200_launch(adadelta_finalize_kernel, dim3(grid), dim3(FIN_THREADS), 0, s, p, g, v, u,
                          bucket0_done ? 0 : (int)(b1_off / 4), (int)b1_off, nchunks, first_partial, segs,
                          (B200Ctrl*)ctrl, rho, eps, advance, done_counter));
   b200_count_launch();

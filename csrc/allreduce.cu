@@ -153,50 +153,83 @@ fused_allreduce_kernel(const CommArgs* __restrict__ table, uint32_t token, float
 #pragma unroll
   for (int q = 0; q < SYMM_MAX_WORLD; ++q) { gp[q] = a.grad[q < W ? q : 0]; pp[q] = a.param[q < W ? q : 0]; }
 
-  comm_barrier(a, a.channel, 0, tok);
-
   int lo = 0, hi = a.n4;
   if (MODE >= 1) {
     const int per = (a.n4 + W - 1) / W;
     lo = min(a.n4, r * per);
     hi = min(a.n4, lo + per);
   }
+  // Two elements per thread and round, all their peer loads in flight together: a peer load is a ~2 us round trip
+  // over NVLink, and one element per round made the kernel a chain of such round trips (4 of them at W = 2).  The
+  // local operands of the first round (parameters and Adadelta state of this rank's own slice, which no peer
+  // touches before the barrier) are fetched BEFORE the barrier is waited for.
+  constexpr int U = 2;
   const int stride = gridDim.x * blockDim.x;
-  for (int i = lo + blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += stride) {
-    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+  const int i0 = lo + blockIdx.x * blockDim.x + threadIdx.x;
+  float4 p[U], vv[U], uu[U];
+  auto load_state = [&](int i) {
+#pragma unroll
+    for (int k = 0; k < U; ++k) {
+      const int e = i + k * stride;
+      if (OPT && e < hi) {
+        p[k] = *reinterpret_cast<const float4*>(a.param[r] + 4 * (size_t)e);
+        vv[k] = *reinterpret_cast<const float4*>(a.v + 4 * (size_t)e);
+        uu[k] = *reinterpret_cast<const float4*>(a.u + 4 * (size_t)e);
+      }
+    }
+  };
+  load_state(i0);
+
+  comm_barrier(a, a.channel, 0, tok);
+
+  for (int i = i0; i < hi; i += U * stride) {
+    if (i != i0) load_state(i);
+    float4 s[U];
+#pragma unroll
+    for (int k = 0; k < U; ++k) s[k] = make_float4(0.f, 0.f, 0.f, 0.f);
     if (MODE == 2) {
-      s = multimem_ld_reduce_f4(a.mc_grad + 4 * (size_t)i);  // in-switch reduction (NVLS)
+#pragma unroll
+      for (int k = 0; k < U; ++k)
+        if (i + k * stride < hi) s[k] = multimem_ld_reduce_f4(a.mc_grad + 4 * (size_t)(i + k * stride));  // in-switch reduction (NVLS)
     } else {
 #pragma unroll
       for (int q = 0; q < SYMM_MAX_WORLD; ++q) {
         if (q < W) {  // fixed rank order on every rank: bit-identical sums
-          const float4 g = ld_peer_f4(gp[q] + 4 * (size_t)i);
-          s.x += g.x; s.y += g.y; s.z += g.z; s.w += g.w;
+#pragma unroll
+          for (int k = 0; k < U; ++k) {
+            if (i + k * stride < hi) {
+              const float4 g = ld_peer_f4(gp[q] + 4 * (size_t)(i + k * stride));
+              s[k].x += g.x; s[k].y += g.y; s[k].z += g.z; s[k].w += g.w;
+            }
+          }
         }
       }
     }
-    s.x *= inv_w; s.y *= inv_w; s.z *= inv_w; s.w *= inv_w;
-    float4 out = s;
-    if (OPT) {
-      float4 p = *reinterpret_cast<const float4*>(a.param[r] + 4 * (size_t)i);
-      float4 vv = *reinterpret_cast<const float4*>(a.v + 4 * (size_t)i);
-      float4 uu = *reinterpret_cast<const float4*>(a.u + 4 * (size_t)i);
-      adadelta_update(s.x, p.x, vv.x, uu.x, lr, rho, eps);
-      adadelta_update(s.y, p.y, vv.y, uu.y, lr, rho, eps);
-      adadelta_update(s.z, p.z, vv.z, uu.z, lr, rho, eps);
-      adadelta_update(s.w, p.w, vv.w, uu.w, lr, rho, eps);
-      *reinterpret_cast<float4*>(a.v + 4 * (size_t)i) = vv;
-      *reinterpret_cast<float4*>(a.u + 4 * (size_t)i) = uu;
-      out = p;
-    }
-    if (MODE == 0) {
-      *reinterpret_cast<float4*>(a.param[r] + 4 * (size_t)i) = out;
-    } else if (MODE == 2) {
-      multimem_st_f4(a.mc_param + 4 * (size_t)i, out);  // one store, delivered to every rank
-    } else {
 #pragma unroll
-      for (int q = 0; q < SYMM_MAX_WORLD; ++q)
-        if (q < W) st_peer_f4(pp[q] + 4 * (size_t)i, out);
+    for (int k = 0; k < U; ++k) {
+      const int e = i + k * stride;
+      if (e >= hi) continue;
+      float4 g = s[k];
+      g.x *= inv_w; g.y *= inv_w; g.z *= inv_w; g.w *= inv_w;
+      float4 out = g;
+      if (OPT) {
+        adadelta_update(g.x, p[k].x, vv[k].x, uu[k].x, lr, rho, eps);
+        adadelta_update(g.y, p[k].y, vv[k].y, uu[k].y, lr, rho, eps);
+        adadelta_update(g.z, p[k].z, vv[k].z, uu[k].z, lr, rho, eps);
+        adadelta_update(g.w, p[k].w, vv[k].w, uu[k].w, lr, rho, eps);
+        *reinterpret_cast<float4*>(a.v + 4 * (size_t)e) = vv[k];
+        *reinterpret_cast<float4*>(a.u + 4 * (size_t)e) = uu[k];
+        out = p[k];
+      }
+      if (MODE == 0) {
+        *reinterpret_cast<float4*>(a.param[r] + 4 * (size_t)e) = out;
+      } else if (MODE == 2) {
+        multimem_st_f4(a.mc_param + 4 * (size_t)e, out);  // one store, delivered to every rank
+      } else {
+#pragma unroll
+        for (int q = 0; q < SYMM_MAX_WORLD; ++q)
+          if (q < W) st_peer_f4(pp[q] + 4 * (size_t)e, out);
+      }
     }
   }
   if (MODE == 2) __threadfence_system();  // multimem stores must be performed before the exit signal
@@ -221,7 +254,7 @@ fused_allreduce_kernel(const CommArgs* __restrict__ table, uint32_t token, float
 // in two steps, and treating it as ONE all-reduce at the very end (as DDP does, and as round 1 of this
 // code did) leaves the whole cross-GPU latency exposed after the last backward kernel.  Here:
 //
-//  conv2_reduce_kernel (on the conv2-wgrad branch, under conv2 dgrad / conv1 wgrad): one CTA per 256-float
+//  conv2_reduce_kernel (on the conv2-wgrad branch, under conv2 dgrad / conv1 wgrad): one CTA per 64-float
 //    chunk of conv2.{weight,bias}: sum the wgrad kernel's per-CTA partial rows into this rank's gradient
 //    bucket, tell the chunk's owner, and the owner all-reduces the chunk into EVERY rank's reduced-gradient
 //    buffer R (owner = chunk % W; P2P loads in fixed rank order + P2P stores, or multimem.ld_reduce +
@@ -236,23 +269,23 @@ fused_allreduce_kernel(const CommArgs* __restrict__ table, uint32_t token, float
 // a rank reaches the NEXT step's communication kernels only after its own finalize kernel, so nobody
 // overwrites a gradient chunk or R while a peer may still read the previous step's value.
 template <int MODE>
-__global__ void __launch_bounds__(64 * FIN_SLICES)
+__global__ void __launch_bounds__(FIN_THREADS)
 conv2_reduce_kernel(const CommArgs* __restrict__ table, FinalizeSegs segs, const FinalizeSegs* __restrict__ segs_emul,
                     int channel) {
-  __shared__ float4 red[FIN_SLICES][64];
+  __shared__ float4 red[FIN_SLICES][FIN_COLS];
   pdl_trigger();
   pdl_wait();
   const CommArgs& a = table[blockIdx.y];
   if (segs_emul) segs = segs_emul[blockIdx.y];
   const int W = a.world, r = a.rank;
   const uint32_t tok = (uint32_t)(a.ctrl->step) * 2u + 1u;
-  const int col = threadIdx.x & 63, off = blockIdx.x * 256;
+  const int col = threadIdx.x % FIN_COLS, off = blockIdx.x * FIN_CHUNK;
   const size_t i4 = (size_t)off + 4 * col;
   const float4 t = reduce_partial_chunk(segs, off, red);
-  if (threadIdx.x < 64) *reinterpret_cast<float4*>(const_cast<float*>(a.grad[r]) + i4) = t;
+  if (threadIdx.x < FIN_COLS) *reinterpret_cast<float4*>(const_cast<float*>(a.grad[r]) + i4) = t;
   if (MODE == 0) {
     comm_barrier(a, channel, 0, tok);
-    if (threadIdx.x < 64) {
+    if (threadIdx.x < FIN_COLS) {
       float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
       for (int q = 0; q < SYMM_MAX_WORLD; ++q) {
@@ -267,7 +300,7 @@ conv2_reduce_kernel(const CommArgs* __restrict__ table, FinalizeSegs segs, const
   } else {
     const int owner = blockIdx.x % W;
     comm_signal_owner(a, channel, owner, tok);
-    if (r == owner && threadIdx.x < 64) {
+    if (r == owner && threadIdx.x < FIN_COLS) {
       float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
       if (MODE == 2) {
         s = multimem_ld_reduce_f4(a.mc_grad + i4);  // in-switch reduction (NVLS)
@@ -293,10 +326,10 @@ conv2_reduce_kernel(const CommArgs* __restrict__ table, FinalizeSegs segs, const
   }
 }
 
-__global__ void __launch_bounds__(64 * FIN_SLICES)
+__global__ void __launch_bounds__(FIN_THREADS)
 conv_finalize_kernel(const CommArgs* __restrict__ table, FinalizeSegs segs, const FinalizeSegs* __restrict__ segs_emul,
                      int first_partial, float rho, float eps, int advance, unsigned int* __restrict__ done_counter) {
-  __shared__ float4 red[FIN_SLICES][64];
+  __shared__ float4 red[FIN_SLICES][FIN_COLS];
   pdl_trigger();
   pdl_wait();
   const CommArgs& a = table[blockIdx.y];
@@ -304,15 +337,15 @@ conv_finalize_kernel(const CommArgs* __restrict__ table, FinalizeSegs segs, cons
   const int W = a.world, r = a.rank;
   const uint32_t tok = (uint32_t)(a.ctrl->step) * 2u + 1u;
   const float lr = a.ctrl->lr;
-  const int col = threadIdx.x & 63, off = blockIdx.x * 256;
+  const int col = threadIdx.x % FIN_COLS, off = blockIdx.x * FIN_CHUNK;
   const size_t i4 = (size_t)off + 4 * col;
   const bool partial = (int)blockIdx.x >= first_partial;  // conv1: still partial rows; conv2: already in R
   if (partial) {
     const float4 t = reduce_partial_chunk(segs, off, red);
-    if (threadIdx.x < 64) *reinterpret_cast<float4*>(const_cast<float*>(a.grad[r]) + i4) = t;
+    if (threadIdx.x < FIN_COLS) *reinterpret_cast<float4*>(const_cast<float*>(a.grad[r]) + i4) = t;
   }
   comm_barrier(a, a.channel, 0, tok);  // release is cumulative over the gradient stores above
-  if (threadIdx.x < 64) {
+  if (threadIdx.x < FIN_COLS) {
     float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
     if (partial) {
 #pragma unroll
@@ -451,16 +484,17 @@ int run_plan(const CommPlan* p, int mode, int opt, uint32_t token, int nblocks, 
 }
 
 // conv bucket, both kernels.  which: 0 = conv2_reduce (chunks [0, c2_chunks)), 1 = conv_finalize (all chunks).
-// Emulated plans (slots > 1) launch cooperatively with 256-thread CTAs so that W x chunks CTAs are co-resident.
+// Emulated plans (slots > 1) launch cooperatively: W x chunks CTAs of 256 threads must be co-resident.
 int run_conv_bucket(const CommPlan* p, int which, int mode, const FinalizeSegs& segs, const FinalizeSegs* segs_emul,
                     int c2_chunks, int chunks, int channel_c2, int advance, unsigned int* done_counter, cudaStream_t s) {
   B200_REQUIRE(p && p->has_red, "conv bucket: the plan has no reduced-gradient region");
   B200_REQUIRE(mode >= 0 && mode <= 2 && (mode != 2 || p->has_mc), "conv bucket: bad mode %d", mode);
-  B200_REQUIRE(chunks * 64 == p->n4 && c2_chunks > 0 && c2_chunks < chunks && chunks <= SYMM_MAX_BLOCKS,
+  B200_REQUIRE(chunks * FIN_COLS == p->n4 && c2_chunks > 0 && c2_chunks < chunks && chunks <= SYMM_MAX_BLOCKS,
                "conv bucket: %d chunks (%d of conv2) do not match a plan of %d float4", chunks, c2_chunks, p->n4);
   B200_REQUIRE(channel_c2 >= 0 && channel_c2 < SYMM_CHANNELS, "conv bucket: bad channel");
   const CommArgs* tab = p->dev;
-  const int threads = p->slots > 1 ? 256 : 64 * FIN_SLICES;
+  // emulated ranks: W x chunks CTAs must all be co-resident for the cooperative launch, so they run 4 slices
+  const int threads = p->slots > 1 ? 4 * FIN_COLS : FIN_THREADS;
   FinalizeSegs sg = segs;
   float rho = 0.9f, eps = 1e-6f;
   int first_partial = c2_chunks;
@@ -506,8 +540,8 @@ int hook_bucket_ready(Engine* E, int bucket, cudaStream_t s) {
     // barrier: the finalize kernel's entry barrier orders this kernel's peer accesses (see above).
     // Footprint of the reducer (env-tunable).  Measured at W = 2 (us/step): 64x512 160.8, 37x512 167,
     // 148x512 174, 74x256 172, 148x256 186, 148x128 206 -- few fat CTAs beat one light CTA per SM.
-    static const int nb0 = getenv("B200_DDP_B0_BLOCKS") ? atoi(getenv("B200_DDP_B0_BLOCKS")) : 96;
-    static const int th0 = getenv("B200_DDP_B0_THREADS") ? atoi(getenv("B200_DDP_B0_THREADS")) : 512;
+    static const int nb0 = getenv("B200_DDP_B0_BLOCKS") ? atoi(getenv("B200_DDP_B0_BLOCKS")) : 148;
+    static const int th0 = getenv("B200_DDP_B0_THREADS") ? atoi(getenv("B200_DDP_B0_THREADS")) : 256;
     static const int exit_b = getenv("B200_DDP_EXIT_BARRIER") ? atoi(getenv("B200_DDP_EXIT_BARRIER")) : 0;
     return run_plan(d->plan[0], d->mode[0], 1, 0, min(nb0, SYMM_MAX_BLOCKS), 0.9f, 1e-6f, s, exit_b, th0);
   }
@@ -595,8 +629,8 @@ extern "C" int b200_comm_conv_bucket_emulated(void* plan, int mode, const float*
   B200_CHECK(cudaMalloc(&dev, sizeof(FinalizeSegs) * 2 * p->slots));
   B200_CHECK(cudaMemcpyAsync(dev, h2.data(), sizeof(FinalizeSegs) * p->slots, cudaMemcpyHostToDevice, s));
   B200_CHECK(cudaMemcpyAsync(dev + p->slots, h1.data(), sizeof(FinalizeSegs) * p->slots, cudaMemcpyHostToDevice, s));
-  int r = run_conv_bucket(p, 0, mode, h2[0], dev, 73, 76, CH_CONV2, -1, nullptr, s);
-  if (r == B200_OK) r = run_conv_bucket(p, 1, mode, h1[0], dev + p->slots, 73, 76, CH_CONV2, advance, counters, s);
+  int r = run_conv_bucket(p, 0, mode, h2[0], dev, 18688 / FIN_CHUNK, 19456 / FIN_CHUNK, CH_CONV2, -1, nullptr, s);
+  if (r == B200_OK) r = run_conv_bucket(p, 1, mode, h1[0], dev + p->slots, 18688 / FIN_CHUNK, 19456 / FIN_CHUNK, CH_CONV2, advance, counters, s);
   cudaStreamSynchronize(s);
   cudaFree(dev);
   return r;

@@ -193,28 +193,40 @@ int enqueue_train(Engine* E, const uint8_t* images, const uint8_t* labels, const
     TRYM(E->hooks.bucket_ready(E, 0, s), s);  // bucket 0 (fc1.*, fc2.*) is complete here
     fc_updated = true;
   }
-  // ---- conv2 backward: wgrad on its own branch next to dgrad; both read (dp, argmax) directly
+  // ---- conv2 backward; both kernels read (dp, argmax) directly.
+  // wgrad and dgrad each need nearly all shared memory of an SM, so they never overlap: they run one after the
+  // other in whatever order the block scheduler picks, and with two ranks picking differently every cross-GPU
+  // barrier waits for the slower choice (measured).  The order is therefore fixed: wgrad FIRST on the main stream,
+  // then dgrad; what follows wgrad (partial rows -> gradient -> cross-GPU all-reduce of conv2's 74 KB) forks onto
+  // branch 1 and has all of dgrad + conv1 wgrad (40 us) to hide under.  B200_CONV2_ORDER=0 restores the unordered
+  // two-stream form.
+  static const bool ordered = !(getenv("B200_CONV2_ORDER") && atoi(getenv("B200_CONV2_ORDER")) == 0);
   const long b1 = c.bucket_begin[1];
-  cudaStream_t sc = par ? E->br[1] : s;
-  if (par) B200_CHECK(cudaStreamWaitEvent(sc, E->ev_fcd, 0));
+  cudaStream_t sc = par ? E->br[1] : s;         // stream of the conv2 reduction
+  cudaStream_t swg = (par && !ordered) ? sc : s;  // stream of conv2 wgrad
+  if (par && !ordered) B200_CHECK(cudaStreamWaitEvent(sc, E->ev_fcd, 0));
   int np2 = 0;
   for (int pass = 0; pass < 2; ++pass) {
-    // with branches the critical-path kernel (dgrad) is enqueued first so that it gets the SMs first
-    const bool do_wgrad = (pass == 0) != par;
+    // unordered form: the critical-path kernel (dgrad) is enqueued first
+    const bool do_wgrad = (pass == 0) != (par && !ordered);
     if (E->use_tc & B200_TC_CONV2_BWD) {
       if (do_wgrad) {
-        TRYM(b200_conv2_wgrad_tc(E->dp, E->amax, E->a1, E->c2_part, nullptr, nullptr, batch, sc), sc);
+        TRYM(b200_conv2_wgrad_tc(E->dp, E->amax, E->a1, E->c2_part, nullptr, nullptr, batch, swg), swg);
         np2 = b200_conv2_wgrad_tc_parts(batch);
       } else {
         TRYM(b200_conv2_dgrad_tc(E->dp, E->amax, P + c.offsets[2], E->a1, E->da1, batch, s), s);
       }
     } else {
       if (do_wgrad) {
-        TRYM(b200_conv2_wgrad_simt(E->dp, E->amax, E->a1, E->c2_part, nullptr, nullptr, batch, sc), sc);
+        TRYM(b200_conv2_wgrad_simt(E->dp, E->amax, E->a1, E->c2_part, nullptr, nullptr, batch, swg), swg);
         np2 = min(9 * batch, E->nsm);
       } else {
         TRYM(b200_conv2_dgrad_simt(E->dp, E->amax, P + c.offsets[2], E->a1, E->da1, batch, s), s);
       }
+    }
+    if (do_wgrad && par && ordered) {  // fork: the reduction leaves the main stream right after wgrad
+      B200_CHECK(cudaEventRecord(E->ev_wg, s));
+      B200_CHECK(cudaStreamWaitEvent(sc, E->ev_wg, 0));
     }
   }
   const int c2row = 9 * C2 * C1 + C2;
@@ -333,8 +345,8 @@ extern "C" int b200_engine_create(const B200EngineConfig* cfg, void** out) {
                cfg->offsets[0] > cfg->offsets[3] && cfg->offsets[1] > cfg->offsets[0] &&
                (cfg->bucket_end[1] - cfg->bucket_begin[1]) % 256 == 0 && (cfg->offsets[0] - cfg->bucket_begin[1]) % 256 == 0,
                "engine_create: unexpected conv bucket layout");
-  E->c2_chunks = (int)((cfg->offsets[0] - cfg->bucket_begin[1]) / 256);
-  E->conv_chunks = (int)((cfg->bucket_end[1] - cfg->bucket_begin[1]) / 256);
+  E->c2_chunks = (int)((cfg->offsets[0] - cfg->bucket_begin[1]) / FIN_CHUNK);
+  E->conv_chunks = (int)((cfg->bucket_end[1] - cfg->bucket_begin[1]) / FIN_CHUNK);
   const size_t B = (size_t)cfg->max_batch, T = (size_t)cfg->param_floats;
   int r = B200_OK;
 #define A(ptr, count) if (r == B200_OK) r = dev_alloc(E, &(ptr), (count))
@@ -386,8 +398,16 @@ extern "C" int b200_engine_create(const B200EngineConfig* cfg, void** out) {
   memset(E->loss_ring_host, 0, B200_LOSS_RING * sizeof(float));
   B200_CHECK(cudaHostGetDevicePointer((void**)&E->loss_ring_host_dev, E->loss_ring_host, 0));
   E->branches = !(getenv("B200_NO_BRANCH") && atoi(getenv("B200_NO_BRANCH")) == 1);
-  for (int i = 0; i < 2; ++i) B200_CHECK(cudaStreamCreateWithFlags(&E->br[i], cudaStreamNonBlocking));
-  for (cudaEvent_t* e : {&E->ev_head, &E->ev_fcw, &E->ev_fcd, &E->ev_fcu, &E->ev_c2w})
+  // Branch streams get the LOWEST priority and the engine's own stream (created by the caller) should have a higher
+  // one: where a branch kernel and a critical-path kernel compete for SMs (conv2 wgrad vs conv2 dgrad: both need
+  // nearly all shared memory of an SM, so they run one after the other), the block scheduler starts the
+  // critical-path kernel first.  Stream priorities are recorded in the captured graph's kernel nodes.
+  int prio_lo = 0, prio_hi = 0;
+  B200_CHECK(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+  static const bool flat = getenv("B200_FLAT_PRIORITY") != nullptr;  // diagnostics
+  for (int i = 0; i < 2; ++i)
+    B200_CHECK(cudaStreamCreateWithPriority(&E->br[i], cudaStreamNonBlocking, flat ? prio_hi : prio_lo));
+  for (cudaEvent_t* e : {&E->ev_head, &E->ev_fcw, &E->ev_fcd, &E->ev_fcu, &E->ev_c2w, &E->ev_wg})
     B200_CHECK(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
   const float inv_w = 1.0f / (float)(cfg->world > 0 ? cfg->world : 1);
   TRY(b200_ctrl_set(E->ctrl, 0, cfg->seed, 0, 3, 1.0f, inv_w, nullptr));
@@ -407,7 +427,7 @@ extern "C" int b200_engine_destroy(void* engine) {
   }
   if (E->hooks.destroy) E->hooks.destroy(E);
   for (int i = 0; i < 2; ++i) if (E->br[i]) cudaStreamDestroy(E->br[i]);
-  for (cudaEvent_t e : {E->ev_head, E->ev_fcw, E->ev_fcd, E->ev_fcu, E->ev_c2w}) if (e) cudaEventDestroy(e);
+  for (cudaEvent_t e : {E->ev_head, E->ev_fcw, E->ev_fcd, E->ev_fcu, E->ev_c2w, E->ev_wg}) if (e) cudaEventDestroy(e);
   if (E->copy_stream) {
     cudaStreamDestroy(E->copy_stream);
     for (int i = 0; i < 2; ++i) { cudaEventDestroy(E->ev_copied[i]); cudaEventDestroy(E->ev_consumed[i]); }

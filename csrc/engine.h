@@ -12,18 +12,22 @@ enum { B200_TC_CONV2_FWD = 1 /* conv1+conv2 forward in one kernel (tc_conv2_v4.c
        B200_TC_FC1_FP32 = 16 /* fc1 GEMMs as 3xTF32 split-operand products (fp32-class, the reference's SGEMM accuracy) */ };
 
 // Where conv-bucket gradients still sit as per-CTA partial sums when a backward kernel ends.  The kernels
-// that consume them (adadelta.cu / allreduce.cu) run one CTA per 256-float chunk of the bucket and reduce
+// that consume them (adadelta.cu / allreduce.cu) run one CTA per FIN_CHUNK-float chunk of the bucket and reduce
 // the partial rows themselves in a fixed order, so no separate reduction launches sit on the critical
 // path.  dst_off: float offset of the segment inside the bucket (a multiple of 256); n: floats per row.
-constexpr int FIN_SLICES = 16;  // those kernels run 64 float4 columns x (blockDim/64 <= FIN_SLICES) row slices per CTA
+// Those kernels run FIN_COLS float4 columns x FIN_SLICES row slices per CTA: a CTA owns a chunk of FIN_CHUNK = 64
+// floats.  256 threads and 4 KB of shared memory are small enough to be co-resident with a persistent conv2
+// backward CTA (222 KB of shared memory), so they can run UNDER the conv backward instead of queueing behind it,
+// and 292 CTAs for conv2's 18688 floats spread the 11 MB of partial rows over every SM.
+constexpr int FIN_COLS = 16, FIN_SLICES = 16, FIN_CHUNK = 4 * FIN_COLS, FIN_THREADS = FIN_COLS * FIN_SLICES;
 struct FinalizeSegs {
   struct Seg { const float* src; int nparts, stride, n, dst_off; } seg[2];
 };
 #ifdef __CUDACC__
 // sum over the partial rows of the segment(s) covering floats [off + 4*col, +4) of the bucket; every thread of
-// the CTA calls this (col = threadIdx & 63, slice = threadIdx >> 6), the total is returned to slice 0
-__device__ __forceinline__ float4 reduce_partial_chunk(const FinalizeSegs& segs, int off, float4 (*red)[64]) {
-  const int col = threadIdx.x & 63, slice = threadIdx.x >> 6, nsl = blockDim.x >> 6;
+// the CTA calls this (col = threadIdx % FIN_COLS, slice = threadIdx / FIN_COLS), the total is returned to slice 0
+__device__ __forceinline__ float4 reduce_partial_chunk(const FinalizeSegs& segs, int off, float4 (*red)[FIN_COLS]) {
+  const int col = threadIdx.x % FIN_COLS, slice = threadIdx.x / FIN_COLS, nsl = blockDim.x / FIN_COLS;  // <= FIN_SLICES
   float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
   for (int k = 0; k < 2; ++k) {
@@ -105,9 +109,9 @@ struct Engine {
   // events, so the whole step is still one capturable graph): br[0] = head wgrad, fc1 wgrad and the
   // fc bucket's Adadelta, br[1] = conv2 wgrad.
   cudaStream_t br[2] = {nullptr, nullptr};
-  cudaEvent_t ev_head = nullptr, ev_fcw = nullptr, ev_fcd = nullptr, ev_fcu = nullptr, ev_c2w = nullptr;
+  cudaEvent_t ev_head = nullptr, ev_fcw = nullptr, ev_fcd = nullptr, ev_fcu = nullptr, ev_c2w = nullptr, ev_wg = nullptr;
   bool branches = true;
   EngineHooks hooks;
   FinalizeSegs fin_c2{}, fin_c1{};  // partial rows of conv2 / conv1 wgrad, filled by enqueue_train
-  int c2_chunks = 0, conv_chunks = 0;  // 256-float chunks of conv2.{weight,bias} / of the whole conv bucket
+  int c2_chunks = 0, conv_chunks = 0;  // FIN_CHUNK-float chunks of conv2.{weight,bias} / of the whole conv bucket
 };

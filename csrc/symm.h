@@ -4,7 +4,7 @@
 #include <stdint.h>
 
 constexpr int SYMM_MAX_WORLD = 8;
-constexpr int SYMM_MAX_BLOCKS = 256;   // CTAs per communication kernel
+constexpr int SYMM_MAX_BLOCKS = 512;   // CTAs per communication kernel
 constexpr int SYMM_CHANNELS = 4;       // independent barrier channels (fc bucket, conv bucket, stand-alone calls, conv2 half)
 // flag word index: ((channel * 2 + phase) * SYMM_MAX_BLOCKS + block) * SYMM_MAX_WORLD + source_rank
 constexpr int SYMM_FLAG_WORDS = SYMM_CHANNELS * 2 * SYMM_MAX_BLOCKS * SYMM_MAX_WORLD;

@@ -46,7 +46,10 @@ constexpr int EPI_WARPS = 8, PROD_WARPS = 4;
 constexpr int DG4_THREADS = (EPI_WARPS + PROD_WARPS + 1) * 32;  // 416
 constexpr int DG4_UPT = (9 * WP * 8 + PROD_WARPS * 32 - 1) / (PROD_WARPS * 32);  // 7 work units per producer thread
 
-__global__ void __launch_bounds__(DG4_THREADS, 1)
+// (registers capped at 104: 43 K per CTA leaves room for a co-resident CTA of the small reduction / communication
+// kernels of the step, so those overlap this kernel; uncapped ptxas takes 128 x 416 = 53 K.  A cap of 88 costs this
+// kernel 8 us -- 34.7 instead of 26.4 -- for nothing)
+__global__ void __maxnreg__(104)
 conv2_dgrad_tc_kernel(const __grid_constant__ CUtensorMap mapW, const float* __restrict__ dp,
                        const uint8_t* __restrict__ amax, const float* __restrict__ a1, float* __restrict__ da1,
                        int nitems) {
@@ -244,7 +247,7 @@ constexpr int WG4_THREADS = (WG4_EPI + PROD_WARPS + 1) * 32;  // 288
 constexpr int WG4_UNITS = 4 * WP * 16;                         // (pooled row, pooled column, channel quad) = 768
 constexpr int WG4_UPT = WG4_UNITS / (PROD_WARPS * 32);         // 6 units per producer thread
 
-__global__ void __launch_bounds__(WG4_THREADS, 1)
+__global__ void __maxnreg__(80)  // register cap, see the dgrad kernel
 conv2_wgrad_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const float* __restrict__ dp,
                        const uint8_t* __restrict__ amax, float* __restrict__ part, int nitems) {
   extern __shared__ uint8_t smem_raw[];

@@ -62,7 +62,9 @@ class NativeEngine:
         self.lib = N.lib()
         self.layout = ParamLayout()
         self.device = torch.cuda.current_device() if device is None else device
-        self.stream = torch.cuda.Stream(device=self.device)
+        # highest priority: the engine's branch streams (csrc/engine.cu) run at the lowest, so that critical-path
+        # kernels get the SMs first wherever the two compete
+        self.stream = torch.cuda.Stream(device=self.device, priority=-5)
         self.max_batch, self.world, self.rank = max_batch, world, rank
         cfg = N.EngineConfig()
         cfg.device, cfg.max_batch, cfg.world, cfg.rank, cfg.seed = self.device, max_batch, world, rank, seed

@@ -10,7 +10,7 @@ for path in sys.argv[1:]:
         if row.get('Metric Name') == 'gpu__time_duration.sum':
             name = row['Kernel Name'].replace('<unnamed>::', '').replace('void ', '')
             rows.append((name[:64], float(row['Metric Value'].replace(',', '')), row['Grid Size'], row['Block Size']))
-    idx = [i for i, x in enumerate(rows) if x[0].startswith('conv12') or x[0].startswith('conv1_fwd')]
+    idx = [i for i, x in enumerate(rows) if x[0].startswith('conv12') or x[0].startswith('conv1_fwd') or (x[0].startswith('conv_fwd_tc_kernel') and ', 1>' in x[0])]
     print(path, 'rows', len(rows))
     if len(idx) < 2:
         continue
