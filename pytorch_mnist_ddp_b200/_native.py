@@ -51,7 +51,9 @@ def _fingerprint() -> str:
                 h.update(f.encode())
                 with open(os.path.join(d, f), "rb") as fh:
                     h.update(fh.read())
-    h.update(" ".join(NVCC_FLAGS).encode())
+    # the flags without the checkout's absolute include path: the library built here must still count as fresh
+    # when the tree is copied to another directory (the GPU box)
+    h.update(" ".join(f for f in NVCC_FLAGS if f != INCLUDE).encode())
     return h.hexdigest()
 
 
@@ -63,15 +65,32 @@ def is_fresh() -> bool:
 
 
 def build(force: bool = False, verbose: bool = False) -> str:
-    """Compile every csrc/*.cu for sm_100a and link the shared library.  Returns its path."""
+    """Compile every csrc/*.cu for sm_100a and link the shared library.  Returns its path.
+
+    Safe under torchrun: ranks serialise on a lock file, whoever gets it first builds (objects in a private
+    directory, the library written under a temporary name and renamed into place), the others find it fresh."""
     if not force and is_fresh():
         return LIBPATH
     os.makedirs(BUILD, exist_ok=True)
     os.makedirs(LIBDIR, exist_ok=True)
+    import fcntl
+    with open(os.path.join(LIBDIR, ".build.lock"), "w") as lock:
+        fcntl.flock(lock, fcntl.LOCK_EX)
+        try:
+            if not force and is_fresh():  # another process built it while this one waited
+                return LIBPATH
+            return _build_locked(verbose)
+        finally:
+            fcntl.flock(lock, fcntl.LOCK_UN)
+
+
+def _build_locked(verbose: bool) -> str:
     nvcc = _nvcc()
+    objdir = os.path.join(BUILD, f"obj.{os.getpid()}")
+    os.makedirs(objdir, exist_ok=True)
 
     def compile_one(src: str) -> str:
-        obj = os.path.join(BUILD, src[:-3] + ".o")
+        obj = os.path.join(objdir, src[:-3] + ".o")
         cmd = [nvcc, *NVCC_FLAGS, "-c", os.path.join(CSRC, src), "-o", obj]
         if verbose:
             cmd.insert(1, "-Xptxas=-v")
@@ -84,12 +103,17 @@ def build(force: bool = False, verbose: bool = False) -> str:
 
     with ThreadPoolExecutor(max_workers=min(8, os.cpu_count() or 2)) as ex:
         objs = list(ex.map(compile_one, sources()))
-    link = [nvcc, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", LIBPATH, *objs]
+    tmp = LIBPATH + f".tmp.{os.getpid()}"
+    link = [nvcc, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", tmp, *objs]
     res = subprocess.run(link, capture_output=True, text=True)
     if res.returncode != 0:
         raise RuntimeError(f"link failed:\n{res.stdout}\n{res.stderr}")
-    with open(STAMP, "w") as f:
+    os.replace(tmp, LIBPATH)  # atomic: nobody ever maps a half-written library
+    with open(STAMP + ".tmp", "w") as f:
         f.write(_fingerprint())
+    os.replace(STAMP + ".tmp", STAMP)
+    import shutil
+    shutil.rmtree(objdir, ignore_errors=True)
     return LIBPATH
 
 
@@ -184,9 +208,14 @@ def lib() -> ctypes.CDLL:
     if not is_fresh():
         try:
             path = build()
-        except Exception as e:  # a stale-but-present library is still usable on a box without nvcc
-            if not os.path.isfile(LIBPATH):
-                raise NativeError(f"libb200mnist.so is not built and cannot be built here: {e}") from e
+        except Exception as e:
+            # A library that does not match csrc/ would silently run other kernels than the ones in the tree: refuse,
+            # unless the caller says that is what they want (a deployment box without nvcc).
+            if os.path.isfile(LIBPATH) and os.environ.get("B200_ALLOW_STALE_LIB") == "1":
+                sys.stderr.write(f"[b200] WARNING: using a libb200mnist.so that does not match the sources ({e})\n")
+            else:
+                raise NativeError("libb200mnist.so is missing or older than csrc/ and cannot be rebuilt here "
+                                  f"(set B200_ALLOW_STALE_LIB=1 to load a stale library anyway): {e}") from e
     L = ctypes.CDLL(path)
     L.b200_last_error.restype = ctypes.c_char_p
     L.b200_comm_fault_message.restype = ctypes.c_char_p

@@ -172,6 +172,13 @@ def test_multi_gpu_ddp_equivalence(comm, world):
     if torch.cuda.device_count() < world:
         pytest.skip(f"needs >= {world} GPUs")
     res = _torchrun(world, ["tests/ddp_worker.py", "--comm", comm])
+    try:  # keep every rank's output where a GPU job's artefacts are collected
+        os.makedirs(os.path.join(ROOT, "gpurun_out", "ddp_logs"), exist_ok=True)
+        with open(os.path.join(ROOT, "gpurun_out", "ddp_logs", f"ddp_worker_{comm}_{world}.log"), "w") as f:
+            f.write(res.stdout + "\n---- stderr ----\n" + res.stderr)
+    except OSError:
+        pass
+    print("\n".join(l for l in res.stdout.splitlines() if "DDP-vs-single" in l or "loss" in l))
     if comm == "nvls" and "NVLS unavailable" in res.stdout + res.stderr:
         pytest.skip("no multicast mapping on this host")
     assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
