@@ -260,14 +260,21 @@ fused_allreduce_kernel(const CommArgs* __restrict__ table, uint32_t token, float
 //    buffer R (owner = chunk % W; P2P loads in fixed rank order + P2P stores, or multimem.ld_reduce +
 //    multimem.st through the NVSwitch).  One-shot mode: every rank sums the chunk itself into its own R.
 //    The parameters are not touched here: conv2 dgrad is still reading conv2.weight on every rank.
-//  conv_finalize_kernel (last kernel of the step): conv1's chunks (3 of them) are reduced from their
-//    partial rows, exchanged one-shot (every rank reads all W copies in rank order: bit-identical sums and
-//    no second barrier), conv2's chunks are read back from R; then 1/W is already applied, Adadelta runs
-//    on the whole conv bucket, and the last CTA advances the step counter.
-// Ordering without exit barriers: the finalize kernel's entry barrier is passed only when every rank has
-// finished its conv2_reduce (and fc-bucket) kernel, so R and the two-shot parameter stores have landed;
+//    Each owner finally raises a per-chunk "R complete" flag on every rank.
+//  conv_finalize_kernel (last kernel of the step): conv1's chunks (5 of 64 floats) are reduced from their
+//    partial rows and exchanged one-shot behind an all-to-all barrier (every rank reads all W copies in rank
+//    order: bit-identical sums, no second barrier); conv2's chunks only poll their LOCAL "R complete" flag and
+//    read R; Adadelta runs on the whole conv bucket, and the last CTA advances the step counter.
+// Ordering without exit barriers: the conv1 CTAs' all-to-all barrier is passed only when every rank has reached
+// its finalize kernel, i.e. has finished its conv2_reduce and fc-bucket kernels, so all two-shot stores have landed;
 // a rank reaches the NEXT step's communication kernels only after its own finalize kernel, so nobody
 // overwrites a gradient chunk or R while a peer may still read the previous step's value.
+// "chunk c of R is complete on this rank": written by the chunk's owner (or by the rank itself in one-shot mode) at
+// the end of conv2_reduce_kernel, waited for by conv_finalize_kernel.  Phase-1 slot of the conv2 channel.
+__device__ __forceinline__ int r_done_index(int channel, int chunk, int owner) {
+  return ((channel * 2 + 1) * SYMM_MAX_BLOCKS + chunk) * SYMM_MAX_WORLD + owner;
+}
+
 template <int MODE>
 __global__ void __launch_bounds__(FIN_THREADS)
 conv2_reduce_kernel(const CommArgs* __restrict__ table, FinalizeSegs segs, const FinalizeSegs* __restrict__ segs_emul,
@@ -297,6 +304,8 @@ conv2_reduce_kernel(const CommArgs* __restrict__ table, FinalizeSegs segs, const
       s.x *= a.inv_world; s.y *= a.inv_world; s.z *= a.inv_world; s.w *= a.inv_world;
       *reinterpret_cast<float4*>(a.red[r] + i4) = s;
     }
+    __syncthreads();
+    if (threadIdx.x == 0) st_release_sys(a.flags[r] + r_done_index(channel, blockIdx.x, r), tok);  // R chunk complete here
   } else {
     const int owner = blockIdx.x % W;
     comm_signal_owner(a, channel, owner, tok);
@@ -323,12 +332,22 @@ conv2_reduce_kernel(const CommArgs* __restrict__ table, FinalizeSegs segs, const
           if (q < W) st_peer_f4(a.red[q] + i4, s);
       }
     }
+    if (r == owner) {  // tell every rank that its copy of this chunk of R is complete (release: after the stores above)
+      __syncthreads();
+      if ((int)threadIdx.x < W) st_release_sys(a.flags[threadIdx.x] + r_done_index(channel, blockIdx.x, owner), tok);
+    }
   }
 }
 
+// Last kernel of the step.  CTAs [0, n_c2) each take blockDim/FIN_COLS conv2 chunks: wait for the chunk's "R
+// complete" flag (a LOCAL poll, normally long satisfied: conv2_reduce ran under the conv backward), read the reduced
+// gradient from R, Adadelta.  The remaining CTAs own one conv1 chunk each: reduce its partial rows, exchange one-shot
+// behind an all-to-all barrier, Adadelta.  Only those few CTAs talk to the peers at the end of the step (5 x (W-1)
+// flag stores per rank instead of one barrier per chunk of the whole bucket).
 __global__ void __launch_bounds__(FIN_THREADS)
 conv_finalize_kernel(const CommArgs* __restrict__ table, FinalizeSegs segs, const FinalizeSegs* __restrict__ segs_emul,
-                     int first_partial, float rho, float eps, int advance, unsigned int* __restrict__ done_counter) {
+                     int c2_chunks, int n_c2, int channel_c2, int owner_mod, float rho, float eps, int advance,
+                     unsigned int* __restrict__ done_counter) {
   __shared__ float4 red[FIN_SLICES][FIN_COLS];
   pdl_trigger();
   pdl_wait();
@@ -337,17 +356,29 @@ conv_finalize_kernel(const CommArgs* __restrict__ table, FinalizeSegs segs, cons
   const int W = a.world, r = a.rank;
   const uint32_t tok = (uint32_t)(a.ctrl->step) * 2u + 1u;
   const float lr = a.ctrl->lr;
-  const int col = threadIdx.x % FIN_COLS, off = blockIdx.x * FIN_CHUNK;
-  const size_t i4 = (size_t)off + 4 * col;
-  const bool partial = (int)blockIdx.x >= first_partial;  // conv1: still partial rows; conv2: already in R
-  if (partial) {
+  const int col = threadIdx.x % FIN_COLS;
+  float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+  size_t i4 = 0;
+  bool active = false;
+  if ((int)blockIdx.x < n_c2) {
+    const int per = blockDim.x / FIN_COLS;
+    const int chunk = blockIdx.x * per + threadIdx.x / FIN_COLS;
+    active = chunk < c2_chunks;
+    i4 = (size_t)chunk * FIN_CHUNK + 4 * col;
+    if (active && col == 0) {
+      const int owner = owner_mod ? chunk % W : r;
+      comm_wait(a, a.flags[r] + r_done_index(channel_c2, chunk, owner), tok, 1, owner);
+    }
+    __syncwarp();  // the FIN_COLS = 16 lanes of a chunk sit in one warp; lane `col == 0` has acquired it for them
+    if (active) s = ld_peer_f4(a.red[r] + i4);
+  } else {
+    const int chunk = c2_chunks + ((int)blockIdx.x - n_c2), off = chunk * FIN_CHUNK;
+    i4 = (size_t)off + 4 * col;
     const float4 t = reduce_partial_chunk(segs, off, red);
     if (threadIdx.x < FIN_COLS) *reinterpret_cast<float4*>(const_cast<float*>(a.grad[r]) + i4) = t;
-  }
-  comm_barrier(a, a.channel, 0, tok);  // release is cumulative over the gradient stores above
-  if (threadIdx.x < FIN_COLS) {
-    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (partial) {
+    comm_barrier(a, a.channel, 0, tok);  // release is cumulative over the gradient stores above
+    active = threadIdx.x < FIN_COLS;
+    if (active) {
 #pragma unroll
       for (int q = 0; q < SYMM_MAX_WORLD; ++q) {
         if (q < W) {
@@ -356,9 +387,9 @@ conv_finalize_kernel(const CommArgs* __restrict__ table, FinalizeSegs segs, cons
         }
       }
       s.x *= a.inv_world; s.y *= a.inv_world; s.z *= a.inv_world; s.w *= a.inv_world;
-    } else {
-      s = ld_peer_f4(a.red[r] + i4);  // written by the chunk's owner during conv2_reduce_kernel
     }
+  }
+  if (active) {
     float4 p = *reinterpret_cast<const float4*>(a.param[r] + i4);
     float4 vv = *reinterpret_cast<const float4*>(a.v + i4);
     float4 uu = *reinterpret_cast<const float4*>(a.u + i4);
@@ -497,7 +528,6 @@ int run_conv_bucket(const CommPlan* p, int which, int mode, const FinalizeSegs& 
   const int threads = p->slots > 1 ? 4 * FIN_COLS : FIN_THREADS;
   FinalizeSegs sg = segs;
   float rho = 0.9f, eps = 1e-6f;
-  int first_partial = c2_chunks;
   if (which == 0) {
     dim3 grid(c2_chunks, p->slots);
     if (p->slots == 1) {
@@ -511,13 +541,15 @@ int run_conv_bucket(const CommPlan* p, int which, int mode, const FinalizeSegs& 
       B200_CHECK(cudaLaunchCooperativeKernel(fn, grid, dim3(threads), args, 0, s));
     }
   } else {
-    dim3 grid(chunks, p->slots);
+    const int per = threads / FIN_COLS;
+    int n_c2 = (c2_chunks + per - 1) / per, owner_mod = mode == 0 ? 0 : 1;
+    dim3 grid(n_c2 + (chunks - c2_chunks), p->slots);
     if (p->slots == 1) {
-      B200_CHECK(b200_launch(conv_finalize_kernel, grid, dim3(threads), 0, s, tab, sg, segs_emul, first_partial, rho, eps,
-                             advance, done_counter));
+      B200_CHECK(b200_launch(conv_finalize_kernel, grid, dim3(threads), 0, s, tab, sg, segs_emul, c2_chunks, n_c2, channel_c2,
+                             owner_mod, rho, eps, advance, done_counter));
     } else {
-      void* args[] = {(void*)&tab, (void*)&sg, (void*)&segs_emul, (void*)&first_partial, (void*)&rho, (void*)&eps,
-                      (void*)&advance, (void*)&done_counter};
+      void* args[] = {(void*)&tab, (void*)&sg, (void*)&segs_emul, (void*)&c2_chunks, (void*)&n_c2, (void*)&channel_c2,
+                      (void*)&owner_mod, (void*)&rho, (void*)&eps, (void*)&advance, (void*)&done_counter};
       B200_CHECK(cudaLaunchCooperativeKernel((const void*)conv_finalize_kernel, grid, dim3(threads), args, 0, s));
     }
   }

@@ -59,6 +59,10 @@ def build_parser(ddp: bool) -> argparse.ArgumentParser:
                    help="launch kernels eagerly instead of replaying the step CUDA graph")
     g.add_argument("--eval-all-ranks", action="store_true", default=False,
                    help="run the eval pass on every rank (the reference runs it on rank 0 only)")
+    g.add_argument("--require-real-data", action="store_true", default=False,
+                   help="fail if the MNIST idx files are missing instead of training on synthetic data")
+    g.add_argument("--verify-replicas", type=int, default=0, metavar="N",
+                   help="every N optimizer steps compare all ranks' parameters bit for bit (0 = off)")
     return p
 
 
@@ -72,7 +76,8 @@ def _make_backend(args, use_cuda: bool, train, test, info: DistInfo):
         from .engine import B200Backend  # imports (and if needed builds) the native library
         return B200Backend(train, test, info, lr=args.lr, seed=args.seed, comm=args.comm,
                            use_graph=not args.no_graph,
-                           max_batch=max(args.batch_size, args.test_batch_size))
+                           max_batch=max(args.batch_size, args.test_batch_size),
+                           verify_replicas=args.verify_replicas)
     return TorchBackend(train, test, info, lr=args.lr, device="cuda" if use_cuda else "cpu")
 
 
@@ -84,8 +89,8 @@ def _run(args, ddp: bool) -> None:
         info = DistInfo()
     torch.manual_seed(args.seed)  # same seed on every rank (mnist_ddp.py:140)
 
-    train = load_split(args.data_root, True, announce=info.is_main)
-    test = load_split(args.data_root, False)
+    train = load_split(args.data_root, True, announce=info.is_main, require_real=args.require_real_data)
+    test = load_split(args.data_root, False, require_real=args.require_real_data)
     backend = _make_backend(args, use_cuda, train, test, info)
     if args.load_model:
         backend.load_state_dict(checkpoint.load(args.load_model))

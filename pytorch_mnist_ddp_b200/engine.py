@@ -34,6 +34,7 @@ LOSS_RING = 1024
 TC_CONV2_FWD, TC_FC1_FWD, TC_FC1_BWD, TC_CONV2_BWD, TC_FC1_FP32 = 1, 2, 4, 8, 16
 TC_ALL = 15              # every layer on tensor cores, fc1 in single-pass TF32
 DEFAULT_TC = TC_ALL | TC_FC1_FP32
+_NVTX_STEPS = os.environ.get("B200_NVTX") == "1"
 
 
 def default_tc_mask() -> int:
@@ -106,7 +107,15 @@ class NativeEngine:
         return torch.cuda.stream(self.stream)
 
     def synchronize(self) -> None:
-        self.stream.synchronize()
+        try:
+            self.stream.synchronize()
+        except RuntimeError as e:
+            # a cross-GPU barrier that gave up on a lost peer traps; say who waited for whom instead of only
+            # "unspecified launch failure"
+            fault = self.lib.b200_comm_fault_message().decode()
+            if fault:
+                raise N.NativeError(f"{fault} [{e}]") from e
+            raise
 
     def buffer(self, which: int, dtype: torch.dtype, shape: Optional[Tuple[int, ...]] = None) -> torch.Tensor:
         p, nb = ctypes.c_void_p(), ctypes.c_size_t()
@@ -163,7 +172,11 @@ class NativeEngine:
         N.check(self.lib.b200_engine_set_dropout(self.handle, int(on), self._s()))
 
     def train_step(self, batch: int, use_graph: bool = True) -> int:
+        if _NVTX_STEPS:  # B200_NVTX=1: one NVTX range per optimizer step (epoch / train / test ranges are always on)
+            torch.cuda.nvtx.range_push(f"step {self.steps}")
         N.check(self.lib.b200_engine_train_step(self.handle, batch, int(use_graph), self._s()))
+        if _NVTX_STEPS:
+            torch.cuda.nvtx.range_pop()
         self.steps += 1
         return self.steps - 1
 
@@ -221,8 +234,9 @@ class B200Backend:
     name = "b200"
 
     def __init__(self, train: MnistSplit, test: MnistSplit, info: DistInfo, lr: float, seed: int = 1,
-                 comm: str = "auto", use_graph: bool = True, max_batch: int = 4096) -> None:
+                 comm: str = "auto", use_graph: bool = True, max_batch: int = 4096, verify_replicas: int = 0) -> None:
         self.info = info
+        self.verify_replicas = int(verify_replicas)
         self.use_graph = use_graph
         self.train_split, self.test_split = train, test
         world = info.world_size if info.distributed else 1
@@ -273,6 +287,11 @@ class B200Backend:
         s = self.engine.train_step(bsz, self.use_graph)
         if self._nccl_baseline:
             self._nccl_reduce_and_update(bsz)
+        if self.verify_replicas and self.ddp is not None and (s + 1) % self.verify_replicas == 0:
+            drift = self.ddp.replica_drift()  # collective: every rank gets here at the same step
+            if drift != 0.0:
+                raise N.NativeError(f"replicas diverged at step {s}: max |p_rank - p_rank0| = {drift} "
+                                    f"(--comm {self.ddp.mode}); the fused reduction must keep them bit-identical")
         return s
 
     def step_host(self, images_u8: torch.Tensor, labels_u8: torch.Tensor) -> int:

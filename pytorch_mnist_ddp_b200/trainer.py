@@ -129,7 +129,14 @@ def fit(args, backend, train: MnistSplit, test: MnistSplit, info: DistInfo, *,
     stats: Dict[str, float] = {"steps": 0}
     t_train = 0.0
     last_eval: Tuple[float, int] = (float("nan"), 0)
+    # NVTX ranges around every epoch, its training loop and its evaluation pass: they show up in
+    # nsys / ncu timelines; a no-op without CUDA
+    nvtx = getattr(backend, "name", "") == "b200" and torch.cuda.is_available()
+    push = torch.cuda.nvtx.range_push if nvtx else (lambda name: None)
+    pop = torch.cuda.nvtx.range_pop if nvtx else (lambda: None)
     for epoch in range(1, args.epochs + 1):
+        push(f"epoch {epoch}")
+        push("train")
         samplers.draw_loader_seed()  # iter(train_loader)
         if sampler_mode == "distributed":
             idx = samplers.distributed_indices(n, world, info.rank, epoch)  # set_epoch(epoch)
@@ -157,14 +164,18 @@ def fit(args, backend, train: MnistSplit, test: MnistSplit, info: DistInfo, *,
         while pending:
             _emit(args, epoch, pending.pop(0), world, n, n_batches, backend, info)
         t_train += time.perf_counter() - t0
+        pop()
         if info.is_main or eval_all_ranks:
+            push("test")
             samplers.draw_loader_seed()  # iter(test_loader)
             nll, correct = backend.evaluate(test, args.test_batch_size)
             last_eval = (nll / len(test), correct)
             if info.is_main:
                 print(logfmt.test_line(nll / len(test), correct, len(test)))
+            pop()
         lr = lr * args.gamma  # StepLR(step_size=1), stepped after eval (mnist_ddp.py:189)
         backend.set_lr(lr)
+        pop()
     backend.finish()
     stats.update(train_seconds=t_train, test_loss=last_eval[0], test_correct=last_eval[1])
     return stats

@@ -52,8 +52,14 @@ def synthetic_split(train: bool, n: int | None = None, seed: int = 20181) -> Mni
 
 
 def _read_idx(path: str) -> np.ndarray:
-    with open(path, "rb") as f:
-        data = f.read()
+    """An idx file, plain or gzip-compressed (the form MNIST is distributed in: *-ubyte.gz)."""
+    if path.endswith(".gz"):
+        import gzip
+        with gzip.open(path, "rb") as f:
+            data = f.read()
+    else:
+        with open(path, "rb") as f:
+            data = f.read()
     magic = struct.unpack(">I", data[:4])[0]
     ndim = magic & 0xFF
     if (magic >> 8) != 0x08:
@@ -76,8 +82,16 @@ def raw_dir(root: str) -> str:
     return os.path.join(root, "MNIST", "raw")
 
 
+def _find(root: str, name: str):
+    """The idx file `name` under <root>/MNIST/raw: uncompressed (what torchvision leaves after download), else .gz."""
+    for cand in (os.path.join(raw_dir(root), name), os.path.join(raw_dir(root), name + ".gz")):
+        if os.path.isfile(cand):
+            return cand
+    return None
+
+
 def idx_files_present(root: str) -> bool:
-    return all(os.path.isfile(os.path.join(raw_dir(root), f)) for f in _FILES.values())
+    return all(_find(root, f) is not None for f in _FILES.values())
 
 
 def write_idx_files(root: str, train: MnistSplit, test: MnistSplit) -> None:
@@ -87,13 +101,21 @@ def write_idx_files(root: str, train: MnistSplit, test: MnistSplit) -> None:
         _write_idx(os.path.join(raw_dir(root), _FILES[(is_train, "labels")]), split.labels.numpy())
 
 
-def load_split(root: str, train: bool, announce: bool = False) -> MnistSplit:
-    """idx files if present (same location torchvision uses), else the synthetic split."""
+def load_split(root: str, train: bool, announce: bool = False, require_real: bool = False) -> MnistSplit:
+    """idx files if present (same location torchvision uses; .gz accepted), else the synthetic split.
+
+    The reference downloads MNIST (``download=True``, mnist_ddp.py:157); there is no network here, so a missing
+    dataset falls back to synthetic data -- loudly on rank 0, or not at all with ``require_real`` (--require-real-data)."""
     if idx_files_present(root):
-        d = raw_dir(root)
-        images = _read_idx(os.path.join(d, _FILES[(train, "images")]))
-        labels = _read_idx(os.path.join(d, _FILES[(train, "labels")]))
+        images = _read_idx(_find(root, _FILES[(train, "images")]))
+        labels = _read_idx(_find(root, _FILES[(train, "labels")]))
+        if images.shape[0] != labels.shape[0] or images.shape[1:] != (28, 28):
+            raise ValueError(f"{raw_dir(root)}: idx files disagree (images {images.shape}, labels {labels.shape})")
         return MnistSplit(torch.from_numpy(images), torch.from_numpy(labels), False)
+    if require_real:
+        raise FileNotFoundError(
+            f"--require-real-data: no MNIST idx files ({', '.join(_FILES.values())}, optionally .gz) under "
+            f"{raw_dir(root)}; this build cannot download them (no network)")
     if announce:
         print(f"[data] no idx files under {raw_dir(root)} and no network: using synthetic "
               f"MNIST-shaped data (random pixels/labels)", flush=True)

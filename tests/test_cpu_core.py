@@ -299,3 +299,51 @@ def test_bench_clock_sampler_nvml_path_and_graceful_absence(monkeypatch):
     c.start()
     rec = c.stop()
     assert rec["sm_mhz"] is None and "unavailable" in rec["reasons"][0]
+
+
+def test_gz_idx_files_and_require_real_data(tmp_path):
+    """MNIST is distributed as *-ubyte.gz: the reader takes either form; --require-real-data makes a missing dataset
+    an error instead of a silent switch to synthetic data (mnist_ddp.py:157 downloads, there is no network here)."""
+    import gzip
+    from pytorch_mnist_ddp_b200.utils import data
+    train, test = data.synthetic_split(True, 64), data.synthetic_split(False, 32)
+    root = str(tmp_path / "d")
+    data.write_idx_files(root, train, test)
+    raw = data.raw_dir(root)
+    for f in os.listdir(raw):  # compress two of the four files, leave the others plain
+        if "images" in f:
+            with open(os.path.join(raw, f), "rb") as src, gzip.open(os.path.join(raw, f + ".gz"), "wb") as dst:
+                dst.write(src.read())
+            os.remove(os.path.join(raw, f))
+    assert data.idx_files_present(root)
+    got = data.load_split(root, True, require_real=True)
+    assert not got.synthetic and torch.equal(got.images, train.images) and torch.equal(got.labels, train.labels)
+    empty = str(tmp_path / "nothing")
+    with pytest.raises(FileNotFoundError, match="require-real-data"):
+        data.load_split(empty, True, require_real=True)
+    assert data.load_split(empty, True).synthetic
+
+
+def test_cli_has_the_engine_flags():
+    from pytorch_mnist_ddp_b200.cli import build_parser
+    a = build_parser(True).parse_args(["--require-real-data", "--verify-replicas", "50", "--comm", "nvls"])
+    assert a.require_real_data and a.verify_replicas == 50 and a.comm == "nvls"
+    assert build_parser(False).parse_args([]).verify_replicas == 0
+
+
+def test_bench_arms_share_one_config_and_golden_check():
+    """Both arms of bench.py print the same `config` dict (the driver compares them), and the golden-trajectory check
+    tells a matching run from a wrong one."""
+    import bench
+    c = bench.shared_config(8, 200)
+    assert c["global_batch"] == 1600 and c["parallelism"] == "dp8" and "flushed" in c["l2"]
+    src = open(os.path.join(ROOT, "baseline", "reference_arm.py")).read()
+    assert '"config": shared_config(world, B)' in src and '"metric": METRIC' in src
+    import json
+    golden = json.load(open(bench.GOLDEN))
+    key = "w1_b200_fc3xtf32"
+    assert key in golden and len(golden[key]) == 20
+    ok = bench.check_golden(1, 200, "fc3xtf32", golden[key])
+    bad = bench.check_golden(1, 200, "fc3xtf32", [x + 0.01 for x in golden[key]])
+    none = bench.check_golden(3, 200, "fc3xtf32", golden[key])
+    assert ok["status"] == "ok" and bad["status"] == "MISMATCH" and none["status"].startswith("absent")

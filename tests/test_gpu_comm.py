@@ -183,3 +183,17 @@ def test_multi_gpu_ddp_equivalence(comm, world):
         pytest.skip("no multicast mapping on this host")
     assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
     assert "DDP_EQUIVALENCE_OK" in res.stdout, res.stdout[-3000:]
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs >= 2 GPUs")
+def test_hung_peer_is_reported_with_rank_and_peer():
+    """a peer that stops arriving must end the job with a message naming who waited for whom."""
+    env = dict(os.environ, B200_COMM_TIMEOUT_MS="2500")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr",
+           "127.0.0.1", "--master-port", "29534", "tests/hung_peer_worker.py"]
+    res = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=300, env=env)
+    out = res.stdout + res.stderr
+    line = [l for l in out.splitlines() if "HUNG_PEER_DIAGNOSTIC" in l]
+    assert line, out[-3000:]
+    print(line[0])
+    assert "rank 0 of 2 waited" in line[0] and "for rank 1" in line[0] and "B200_COMM_TIMEOUT_MS" in line[0], line[0]
