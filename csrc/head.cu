@@ -25,37 +25,56 @@ head_fused_kernel(const float* __restrict__ part, int splits, int batch,      //
                   float* __restrict__ dh,        // [B][128]   (train) gradient at fc1's pre-activation
                   float* __restrict__ loss_i,    // [B]        per-sample NLL
                   int* __restrict__ correct_i,   // [B]        (eval) or nullptr
-                  float* __restrict__ logp_out)  // [B][10]    optional log-probs, or nullptr
+                  float* __restrict__ logp_out,  // [B][10]    optional log-probs, or nullptr
+                  int ws)                        // warps per sample (1, 2 or 4)
 {
   __shared__ float w2s[NCLS][FC1_OUT];
   __shared__ float b2s[NCLS];
+  __shared__ float4 zs[8][32];
   pdl_trigger();
   pdl_wait();
   for (int e = threadIdx.x; e < NCLS * FC1_OUT; e += blockDim.x) w2s[e / FC1_OUT][e % FC1_OUT] = w2[e];
   if (threadIdx.x < NCLS) b2s[threadIdx.x] = b2[threadIdx.x];
   __syncthreads();
-  const int lane = threadIdx.x & 31;
-  const int b = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-  if (b >= batch) return;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  // ws warps share one sample's split-K reduction (each sums every ws-th partial, all its loads in flight at once;
+  // the sub-sums are combined in a fixed order through shared memory): with 36 partials a single warp per sample
+  // made this kernel a chain of six dependent L2 round trips.
+  const int spb = (blockDim.x >> 5) / ws;  // samples per block
+  const int sl = warp / ws, sub = warp - sl * ws;
+  const int b = blockIdx.x * spb + sl;
   const int train = ctrl->train;
 
   // ---- fc1 epilogue: reduce split-K partials in a fixed order
-  float4 z = *reinterpret_cast<const float4*>(b1 + lane * 4);
-  {
+  float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (b < batch) {
     const float* src = part + (size_t)b * FC1_OUT + lane * 4;
     const size_t pitch = (size_t)batch * FC1_OUT;
-    int s = 0;
-    for (; s + 6 <= splits; s += 6) {  // six loads in flight, summed in split order
-      float4 p[6];
+    int s = sub;
+    for (; s + 8 * ws < splits; s += 9 * ws) {  // nine loads in flight, summed in split order
+      float4 p[9];
 #pragma unroll
-      for (int j = 0; j < 6; ++j) p[j] = *reinterpret_cast<const float4*>(src + (size_t)(s + j) * pitch);
+      for (int j = 0; j < 9; ++j) p[j] = *reinterpret_cast<const float4*>(src + (size_t)(s + j * ws) * pitch);
 #pragma unroll
-      for (int j = 0; j < 6; ++j) { z.x += p[j].x; z.y += p[j].y; z.z += p[j].z; z.w += p[j].w; }
+      for (int j = 0; j < 9; ++j) { z.x += p[j].x; z.y += p[j].y; z.z += p[j].z; z.w += p[j].w; }
     }
-    for (; s < splits; ++s) {
+    for (; s < splits; s += ws) {
       const float4 p = *reinterpret_cast<const float4*>(src + (size_t)s * pitch);
       z.x += p.x; z.y += p.y; z.z += p.z; z.w += p.w;
     }
+  }
+  if (ws > 1) {
+    zs[warp][lane] = z;
+    __syncthreads();
+    if (sub != 0 || b >= batch) return;
+    z = zs[warp][lane];
+    for (int q = 1; q < ws; ++q) { const float4 v = zs[warp + q][lane]; z.x += v.x; z.y += v.y; z.z += v.z; z.w += v.w; }
+  } else if (b >= batch) {
+    return;
+  }
+  {
+    const float4 bb = *reinterpret_cast<const float4*>(b1 + lane * 4);
+    z.x += bb.x; z.y += bb.y; z.z += bb.z; z.w += bb.w;
   }
   float hv[4] = {fmaxf(z.x, 0.f), fmaxf(z.y, 0.f), fmaxf(z.z, 0.f), fmaxf(z.w, 0.f)};
   if (train & 2) {
@@ -197,10 +216,10 @@ extern "C" int b200_head_fused(const float* part, int splits, int batch, const f
                                float* h, float* dlogits, float* dh, float* loss_i, int* correct_i, float* logp,
                                void* stream) {
   B200_REQUIRE(batch > 0 && splits > 0, "head_fused: bad batch/splits");
-  // small batches: two samples per CTA so that the split-K reduction is spread over ~100 SMs
-  const int warps = batch <= 1024 ? 2 : 8;
-  B200_CHECK(b200_launch(head_fused_kernel, dim3(ceil_div(batch, warps)), dim3(32 * warps), 0, (cudaStream_t)stream, part, splits,
-                         batch, b1, w2, b2, labels, idx, (const B200Ctrl*)ctrl, h, dlogits, dh, loss_i, correct_i, logp));
+  // many partials (small batches): four warps per sample, two samples per CTA; few partials: one warp per sample
+  const int ws = splits >= 8 ? 4 : 1, warps = 8, spb = warps / ws;
+  B200_CHECK(b200_launch(head_fused_kernel, dim3(ceil_div(batch, spb)), dim3(32 * warps), 0, (cudaStream_t)stream, part, splits,
+                         batch, b1, w2, b2, labels, idx, (const B200Ctrl*)ctrl, h, dlogits, dh, loss_i, correct_i, logp, ws));
   b200_count_launch();
   B200_LAUNCH_CHECK();
   return B200_OK;
