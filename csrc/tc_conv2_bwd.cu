@@ -49,7 +49,8 @@ constexpr int DG4_UPT = (9 * WP * 8 + PROD_WARPS * 32 - 1) / (PROD_WARPS * 32); 
 // (registers capped at 104: 43 K per CTA leaves room for a co-resident CTA of the small reduction / communication
 // kernels of the step, so those overlap this kernel; uncapped ptxas takes 128 x 416 = 53 K.  A cap of 88 costs this
 // kernel 8 us -- 34.7 instead of 26.4 -- for nothing)
-__global__ void __maxnreg__(104)
+template <int MAXREG>
+__global__ void __maxnreg__(MAXREG)
 conv2_dgrad_tc_kernel(const __grid_constant__ CUtensorMap mapW, const float* __restrict__ dp,
                        const uint8_t* __restrict__ amax, const float* __restrict__ a1, float* __restrict__ da1,
                        int nitems) {
@@ -247,7 +248,8 @@ constexpr int WG4_THREADS = (WG4_EPI + PROD_WARPS + 1) * 32;  // 288
 constexpr int WG4_UNITS = 4 * WP * 16;                         // (pooled row, pooled column, channel quad) = 768
 constexpr int WG4_UPT = WG4_UNITS / (PROD_WARPS * 32);         // 6 units per producer thread
 
-__global__ void __maxnreg__(80)  // register cap, see the dgrad kernel
+template <int MAXREG>
+__global__ void __maxnreg__(MAXREG)  // register cap: see b200_conv2_dgrad_tc
 conv2_wgrad_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const float* __restrict__ dp,
                        const uint8_t* __restrict__ amax, float* __restrict__ part, int nitems) {
   extern __shared__ uint8_t smem_raw[];
@@ -401,13 +403,23 @@ extern "C" int b200_conv2_dgrad_tc(const float* dp, const uint8_t* amax, const f
   if (r != B200_OK) return r;
   static bool attr = false;
   if (!attr) {
-    B200_CHECK(cudaFuncSetAttribute(conv2_dgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, DG4_SMEM));
+    B200_CHECK(cudaFuncSetAttribute(conv2_dgrad_tc_kernel<104>, cudaFuncAttributeMaxDynamicSharedMemorySize, DG4_SMEM));
+    B200_CHECK(cudaFuncSetAttribute(conv2_dgrad_tc_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, DG4_SMEM));
     attr = true;
   }
   const int nitems = 2 * batch;
   const int grid = min(nitems, b200_sm_count());
-  B200_CHECK(b200_launch(conv2_dgrad_tc_kernel, dim3(grid), dim3(DG4_THREADS), (size_t)DG4_SMEM, (cudaStream_t)stream, mw,
-                         dp, amax, a1, da1, nitems));
+  // Register cap (B200_DGRAD_REGS = 104 | 128).  104 x 416 = 43 K registers would leave room for a co-resident CTA of
+  // the small reduction / communication kernels; 128 is what ptxas takes when left alone (53 K: nothing fits beside
+  // it).  Measured, us/step: 1 GPU 131.6 (104) vs 128.9 (128), 2 GPUs 146.2 vs 144.6 -- the kernel itself loses 4 us
+  // to the cap and the overlap gives less back, so the default is 128.
+  static const int regs = getenv("B200_DGRAD_REGS") ? atoi(getenv("B200_DGRAD_REGS")) : 128;
+  if (regs >= 128)
+    B200_CHECK(b200_launch(conv2_dgrad_tc_kernel<128>, dim3(grid), dim3(DG4_THREADS), (size_t)DG4_SMEM, (cudaStream_t)stream,
+                           mw, dp, amax, a1, da1, nitems));
+  else
+    B200_CHECK(b200_launch(conv2_dgrad_tc_kernel<104>, dim3(grid), dim3(DG4_THREADS), (size_t)DG4_SMEM, (cudaStream_t)stream,
+                           mw, dp, amax, a1, da1, nitems));
   b200_count_launch();
   B200_LAUNCH_CHECK();
   return B200_OK;
@@ -452,13 +464,19 @@ extern "C" int b200_conv2_wgrad_tc(const float* dp, const uint8_t* amax, const f
   if (r != B200_OK) return r;
   static bool attr = false;
   if (!attr) {
-    B200_CHECK(cudaFuncSetAttribute(conv2_wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, WG4_SMEM));
+    B200_CHECK(cudaFuncSetAttribute(conv2_wgrad_tc_kernel<80>, cudaFuncAttributeMaxDynamicSharedMemorySize, WG4_SMEM));
+    B200_CHECK(cudaFuncSetAttribute(conv2_wgrad_tc_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, WG4_SMEM));
     attr = true;
   }
   const int nitems = 3 * batch;
   const int grid = min(nitems, b200_sm_count());
-  B200_CHECK(b200_launch(conv2_wgrad_tc_kernel, dim3(grid), dim3(WG4_THREADS), (size_t)WG4_SMEM, s, ma, dp, amax, part,
-                         nitems));
+  static const int regs = getenv("B200_WGRAD_REGS") ? atoi(getenv("B200_WGRAD_REGS")) : 128;  // 80 | 128; measured 129.4 vs 128.9 us/step
+  if (regs >= 128)
+    B200_CHECK(b200_launch(conv2_wgrad_tc_kernel<128>, dim3(grid), dim3(WG4_THREADS), (size_t)WG4_SMEM, s, ma, dp, amax, part,
+                           nitems));
+  else
+    B200_CHECK(b200_launch(conv2_wgrad_tc_kernel<80>, dim3(grid), dim3(WG4_THREADS), (size_t)WG4_SMEM, s, ma, dp, amax, part,
+                           nitems));
   b200_count_launch();
   if (dw) b200_launch_reduce_partials(dw, part, 9 * C2 * C1, grid, CONV2_PART, s);
   if (db) b200_launch_reduce_partials(db, part + 9 * C2 * C1, C2, grid, CONV2_PART, s);
