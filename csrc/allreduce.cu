@@ -9,19 +9,35 @@
 // ranks get bit-identical results — scales, applies the Adadelta update and writes parameters.
 //
 //   one-shot : every rank reduces the whole bucket and updates its full replica.  (W-1)*S bytes in per
-//              GPU; best for latency-bound sizes (the 75 KB conv bucket, everything at W = 2).
+//              GPU; best for latency-bound sizes.
 //   two-shot : rank r reduces slice r only (reduce-scatter), runs Adadelta on that slice with its own
 //              shard of the optimizer state, and stores the updated PARAMETERS into every peer
 //              (all-gather of parameters, not of gradients).  2*(W-1)/W*S bytes per GPU.
-// Both end with a second barrier: peers may not overwrite their gradient buckets (next backward)
-// until everybody has finished reading them, and in two-shot nobody may start the next forward until
-// every slice of the parameters has landed.
+//   NVLS     : two-shot whose reduce is one multimem.ld_reduce and whose parameter broadcast is one
+//              multimem.st through the NVSwitch (multicast mapping from torch symmetric memory).
+//
+// Kernels of this file:
+//   fused_allreduce_kernel<MODE, OPT>  the fc bucket (4.7 MB): entry barrier, reduce, Adadelta, parameters out.  Runs
+//                                      on the engine's fc branch under the conv backward.
+//   conv2_reduce_kernel<MODE>          conv2's part of the conv bucket: sums the wgrad kernel's partial rows into the
+//                                      gradient, then chunk c is all-reduced by its owner (c % W) into EVERY rank's
+//                                      "reduced" region R, followed by a per-chunk "R complete" flag in every rank.
+//                                      Runs on the conv2-wgrad branch.
+//   conv_finalize_kernel               end of the step: conv2 chunks wait for the LOCAL flag of their owner and apply
+//                                      Adadelta from R; conv1's 5 chunks do a one-shot all-reduce behind the step's only
+//                                      all-to-all barrier.
+// No kernel ends with a barrier.  What makes that safe: a rank's gradient buckets are rewritten
+// only by the next step's backward, which runs after that rank's finalize kernel, and the finalize kernel's all-to-all
+// barrier cannot be passed before every rank has entered it, i.e. before every rank's fc-bucket and conv2-reduce
+// kernels (earlier in that rank's graph) have finished reading peers.
 //
 // Barriers are flag words in the symmetric arena: CTA b of rank r writes a monotonically increasing
 // token (derived from the device-side step counter, so the kernel is CUDA-graph replayable) into slot
-// [b][r] of every peer with st.release.sys and spins with ld.acquire.sys on its own slots.  Spins are
-// bounded and trap.  The kernels also run all ranks inside ONE cooperative launch (blockIdx.y = rank)
-// so that they can be tested on a single GPU.
+// [b][r] of every peer with st.release.sys and spins with ld.acquire.sys on its own slots.  A wait is
+// bounded in TIME (B200_COMM_TIMEOUT_MS, %globaltimer): on expiry the CTA fills in a CommFault record in
+// mapped host memory (rank, peer, channel, expected and seen token) and traps, so the host can name the
+// peer that went missing.  The kernels also run all ranks inside ONE cooperative launch
+// (blockIdx.y = rank) so that they can be tested on a single GPU.
 #include <cstdlib>
 #include <vector>
 
@@ -570,8 +586,8 @@ int hook_bucket_ready(Engine* E, int bucket, cudaStream_t s) {
   if (bucket == 0) {
     // The fc bucket is complete while the conv backward still runs; `s` is the engine's fc branch.  No exit
     // barrier: the finalize kernel's entry barrier orders this kernel's peer accesses (see above).
-    // Footprint of the reducer (env-tunable).  Measured at W = 2 (us/step): 64x512 160.8, 37x512 167,
-    // 148x512 174, 74x256 172, 148x256 186, 148x128 206 -- few fat CTAs beat one light CTA per SM.
+    // Footprint of the reducer (env-tunable).  Measured at W = 2 with the state prefetch in place: 74x512 ... 296x128
+    // all within 148.6 - 150.9 us/step, i.e. no effect; one CTA per SM is the default.
     static const int nb0 = getenv("B200_DDP_B0_BLOCKS") ? atoi(getenv("B200_DDP_B0_BLOCKS")) : 148;
     static const int th0 = getenv("B200_DDP_B0_THREADS") ? atoi(getenv("B200_DDP_B0_THREADS")) : 256;
     static const int exit_b = getenv("B200_DDP_EXIT_BARRIER") ? atoi(getenv("B200_DDP_EXIT_BARRIER")) : 0;
