@@ -382,6 +382,7 @@ int weight_map(const float* w, int atom32, CUtensorMap* out) {
   const void* key = (const char*)w + atom32;  // weights are 256-float aligned: the low bit is free
   auto it = g_wmaps.find(key);
   if (it != g_wmaps.end()) { *out = it->second; return B200_OK; }
+  if (g_wmaps.size() >= 64) g_wmaps.clear();  // bounded: a long-lived host may cycle through many buffers
   CUtensorMap m;
   uint64_t dims[2] = {32, 576}, strides[1] = {128};
   uint32_t box[2] = {32, 64};

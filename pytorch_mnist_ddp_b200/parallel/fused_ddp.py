@@ -4,20 +4,21 @@ What ``DistributedDataParallel(model, device_ids=[gpu])`` (mnist_ddp.py:173) set
 broadcast from rank 0, gradient buckets, an all-reduce per bucket overlapped with backward —
 is rebuilt here on top of csrc/symm.cu and csrc/allreduce.cu:
 
-* `SymmetricArena`: one device allocation per rank holding ``[params | grads | sq_avg | acc_delta]``
-  plus barrier flags, exported with CUDA IPC and mapped into every peer.  ``torch.distributed`` is
+* `SymmetricArena`: one device allocation per rank holding ``[params | grads | sq_avg | acc_delta | reduced conv
+  grads]`` plus barrier flags, exported with CUDA IPC and mapped into every peer.  ``torch.distributed`` is
   used for bootstrap only (all-gather of the 64-byte handles, barriers).
 * `FusedDataParallel.allocate()` hands the arena's buffers to the native engine, so backward
   kernels write gradients straight into the peer-visible bucket (no bucket copy-in / copy-out).
 * `FusedDataParallel.attach()` pulls rank 0's parameters over NVLink (DDP's ``_sync_module_states``)
-  and installs the engine hooks that launch ONE fused all-reduce + 1/W + Adadelta kernel per
-  bucket: the fc bucket on a side stream while the conv backward still runs, the conv bucket at
-  the end (SURVEY N17 bucket layout; section 8 rows 11, 12, 15).
+  and installs the engine hooks that launch the fused all-reduce + 1/W + Adadelta kernels: the fc bucket
+  on a branch stream while the conv backward still runs, conv2's half of the conv bucket on the wgrad branch,
+  conv1's 1.3 KB and the conv-bucket update in the step's last kernel (SURVEY N17 bucket layout; section 8
+  rows 11, 12, 15).
 
 Reduction modes (``--comm``): ``oneshot`` (every rank reduces the whole bucket), ``twoshot``
 (reduce-scatter + sharded Adadelta + parameter all-gather), ``nvls`` = two-shot through the NVSwitch
 (``multimem.ld_reduce`` + ``multimem.st`` on a multicast mapping from torch symmetric memory), ``auto`` =
-``nvls`` when such a mapping exists, ``twoshot`` otherwise.  The mode applies to the fc bucket and to the
+``twoshot`` at 2 ranks, ``nvls`` from 4 ranks on when such a mapping exists (measured), ``twoshot`` otherwise.  The mode applies to the fc bucket and to the
 conv2 half of the conv bucket (reduced on the wgrad branch, under the rest of the backward pass); conv1's
 1.3 KB is exchanged one-shot by the step's last kernel.  ``nccl`` keeps the reference's unfused structure
 (ncclAllReduce + separate Adadelta) as the in-tree baseline, and is what multi-host jobs fall back to.
@@ -203,7 +204,7 @@ class FusedDataParallel:
             # mapping, two-shot over CUDA IPC otherwise.  Every rank must take the same branch, so the outcome of
             # the probe is agreed on with an all-reduce.
             # Measured (us/step, batch 200): at 2 GPUs two-shot 149.0 vs NVLS 160.2 (with one peer the switch adds a
-            # hop and saves no traffic); at 4 GPUs 157.7 vs 157.0, at 8 GPUs 164.6 vs 165.5 (equal).  So NVLS from 4
+            # hop and saves no traffic); at 4 GPUs 157.7 vs 157.0, at 8 GPUs 163.7 vs 160.7.  So NVLS from 4
             # ranks on, where it moves 2*S/W bytes per GPU instead of 2*(W-1)/W*S.
             arena, ok = None, 0
             if os.environ.get("B200_NO_NVLS") != "1" and self.info.world_size >= 4:

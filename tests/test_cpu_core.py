@@ -347,3 +347,39 @@ def test_bench_arms_share_one_config_and_golden_check():
     bad = bench.check_golden(1, 200, "fc3xtf32", [x + 0.01 for x in golden[key]])
     none = bench.check_golden(3, 200, "fc3xtf32", golden[key])
     assert ok["status"] == "ok" and bad["status"] == "MISMATCH" and none["status"].startswith("absent")
+
+
+def test_ranks_on_different_hosts_fall_back_to_nccl(monkeypatch, capsys):
+    """Peer-mapped memory (CUDA IPC, multicast) exists only inside one host, while the reference's env contract reaches
+    across nodes (mnist_ddp.py:16-22,134): allocate() compares host names and switches to --comm nccl with one line."""
+    import torch.distributed as dist
+    from pytorch_mnist_ddp_b200.parallel import fused_ddp
+    from pytorch_mnist_ddp_b200.parallel.dist import DistInfo
+    info = DistInfo(distributed=True, rank=0, world_size=2, gpu=0)
+    hosts = ["node-a", "node-b"]
+
+    def fake_gather(out, mine):
+        out[:] = hosts
+
+    class FakeArena:
+        def base_ptr(self, rank=None):
+            return 4096
+
+    made = {}
+
+    def fake_create(cls, info_, n, exchange=True):
+        made["exchange"], made["floats"] = exchange, n
+        return FakeArena()
+
+    monkeypatch.setattr(dist, "is_initialized", lambda: True)
+    monkeypatch.setattr(dist, "all_gather_object", fake_gather)
+    monkeypatch.setattr(fused_ddp.SymmetricArena, "create", classmethod(fake_create))
+    ddp = fused_ddp.FusedDataParallel(info, "auto")
+    assert not ddp._single_host()
+    ptrs = ddp.allocate(1000)
+    assert ddp.comm == "nccl" and made == {"exchange": False, "floats": 5000}
+    assert ptrs["params"] == 4096 and ptrs["grads0"] == 4096 + 4000 and ptrs["acc_delta"] == 4096 + 12000
+    out = capsys.readouterr().out
+    assert out.count("falling back from --comm auto to --comm nccl") == 1
+    hosts[1] = "node-a"
+    assert fused_ddp.FusedDataParallel(info, "twoshot")._single_host()
