@@ -324,6 +324,10 @@ conv2_reduce_kernel(const CommArgs* __restrict__ table, FinalizeSegs segs, const
     if (threadIdx.x == 0) st_release_sys(a.flags[r] + r_done_index(channel, blockIdx.x, r), tok);  // R chunk complete here
   } else {
     const int owner = blockIdx.x % W;
+    // The peers' chunks reach the owner's multimem load through their st.release.sys; the owner's own chunk was stored
+    // just above through its unicast address, and same-address ordering does not extend to the multicast alias the
+    // switch reads through: make it visible system-wide first.
+    if (MODE == 2 && r == owner && threadIdx.x < FIN_COLS) __threadfence_system();
     comm_signal_owner(a, channel, owner, tok);
     if (r == owner && threadIdx.x < FIN_COLS) {
       float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -531,7 +535,7 @@ int run_plan(const CommPlan* p, int mode, int opt, uint32_t token, int nblocks, 
 }
 
 // conv bucket, both kernels.  which: 0 = conv2_reduce (chunks [0, c2_chunks)), 1 = conv_finalize (all chunks).
-// Emulated plans (slots > 1) launch cooperatively: W x chunks CTAs of 256 threads must be co-resident.
+// Emulated plans (slots > 1) launch cooperatively: W x chunks CTAs must be co-resident, so they use 64-thread CTAs.
 int run_conv_bucket(const CommPlan* p, int which, int mode, const FinalizeSegs& segs, const FinalizeSegs* segs_emul,
                     int c2_chunks, int chunks, int channel_c2, int advance, unsigned int* done_counter, cudaStream_t s) {
   B200_REQUIRE(p && p->has_red, "conv bucket: the plan has no reduced-gradient region");
@@ -540,7 +544,7 @@ int run_conv_bucket(const CommPlan* p, int which, int mode, const FinalizeSegs& 
                "conv bucket: %d chunks (%d of conv2) do not match a plan of %d float4", chunks, c2_chunks, p->n4);
   B200_REQUIRE(channel_c2 >= 0 && channel_c2 < SYMM_CHANNELS, "conv bucket: bad channel");
   const CommArgs* tab = p->dev;
-  // emulated ranks: W x chunks CTAs must all be co-resident for the cooperative launch, so they run 4 slices
+  // emulated ranks: 4 slices per chunk instead of FIN_SLICES (the kernels derive the slice count from blockDim)
   const int threads = p->slots > 1 ? 4 * FIN_COLS : FIN_THREADS;
   FinalizeSegs sg = segs;
   float rho = 0.9f, eps = 1e-6f;
