@@ -723,7 +723,11 @@ extern "C" int b200_ddp_attach(void* engine, void* arena, int mode_bucket0, int 
     const size_t beg = (size_t)E->cfg.bucket_begin[k], n = (size_t)(E->cfg.bucket_end[k] - E->cfg.bucket_begin[k]);
     int r = plan_from_arenas(&a, 1, T + beg, beg, 2 * T + beg, 3 * T + beg, k == 1 ? 4 * T + beg : (size_t)-1, n,
                              k == 0 ? CH_FC : CH_CONV, &ctrl, &d->plan[k]);
-    if (r != B200_OK) return r;
+    if (r != B200_OK) {
+      for (int j = 0; j < k; ++j) { cudaFree(d->plan[j]->dev); delete d->plan[j]; }
+      delete d;
+      return r;
+    }
   }
   E->hooks.state = d;
   E->hooks.bucket_ready = hook_bucket_ready;

@@ -580,10 +580,15 @@ extern "C" int b200_engine_train_step_host(void* engine, const uint8_t* images_h
 // 784-byte memcpy per sample; normalisation happens inside the forward kernel.  The host blocks only if the pinned
 // slot of two steps ago has not been copied out yet.
 extern "C" int b200_engine_train_step_gather(void* engine, const uint8_t* images_host, const uint8_t* labels_host,
-                                             const int32_t* idx_host, int batch, int use_graph, void* stream) {
+                                             int n_samples, const int32_t* idx_host, int batch, int use_graph,
+                                             void* stream) {
   Engine* E = (Engine*)engine;
-  B200_REQUIRE(E && images_host && labels_host && idx_host && batch > 0 && batch <= E->cfg.max_batch,
+  B200_REQUIRE(E && images_host && labels_host && idx_host && n_samples > 0 && batch > 0 && batch <= E->cfg.max_batch,
                "engine_train_step_gather: bad arguments (batch %d, max %d)", batch, E ? E->cfg.max_batch : 0);
+  for (int b = 0; b < batch; ++b)  // a sampler bug must not become a wild host read
+    B200_REQUIRE(idx_host[b] >= 0 && idx_host[b] < n_samples,
+                 "engine_train_step_gather: index %d at position %d is outside the dataset of %d samples", idx_host[b], b,
+                 n_samples);
   const int par = (int)(E->steps & 1);
   if (!E->pin_img[0]) {
     for (int i = 0; i < 2; ++i) {

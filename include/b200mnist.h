@@ -154,9 +154,10 @@ int b200_engine_train_step_host(void* engine, const uint8_t* images_host, const 
                                 int use_graph, void* stream);
 /* the data-loader path: gather `batch` samples of a host-resident uint8 dataset by `idx_host` into the engine's
  * pinned staging memory (a 784-byte memcpy per sample instead of the reference's per-sample transform pipeline,
- * mnist_ddp.py:144-168), then as train_step_host */
+ * mnist_ddp.py:144-168), then as train_step_host.  Every index is checked against `n_samples` (the dataset's size)
+ * before anything is read: an index outside [0, n_samples) returns B200_ERR_ARG */
 int b200_engine_train_step_gather(void* engine, const uint8_t* images_host, const uint8_t* labels_host,
-                                  const int32_t* idx_host, int batch, int use_graph, void* stream);
+                                  int n_samples, const int32_t* idx_host, int batch, int use_graph, void* stream);
 /* forward only on `batch` samples of a split starting at `first`; accumulates sum-NLL / #correct */
 int b200_engine_eval_batch(void* engine, int split, int first, int batch, void* stream);
 int b200_engine_eval_reset(void* engine, void* stream);

@@ -185,7 +185,7 @@ _SIGNATURES = {
     "b200_engine_apply_update": [_vp, _i, _vp],
     "b200_engine_train_step": [_vp, _i, _i, _vp],
     "b200_engine_train_step_host": [_vp, _vp, _vp, _i, _i, _vp],
-    "b200_engine_train_step_gather": [_vp, _vp, _vp, _vp, _i, _i, _vp],
+    "b200_engine_train_step_gather": [_vp, _vp, _vp, _i, _vp, _i, _i, _vp],
     "b200_engine_eval_batch": [_vp, _i, _i, _i, _vp],
     "b200_engine_eval_reset": [_vp, _vp],
     "b200_engine_eval_result": [_vp, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_longlong), _vp],

@@ -193,9 +193,15 @@ class NativeEngine:
         """The data-loader path: `idx_i32` (host int32) selects this step's samples from a HOST-resident uint8
         dataset; they are gathered into pinned staging memory by the native library, copied to the GPU on the copy
         stream (overlapping the previous step) and trained on."""
+        if not (images_u8.dtype == torch.uint8 and labels_u8.dtype == torch.uint8 and idx_i32.dtype == torch.int32
+                and images_u8.device.type == labels_u8.device.type == idx_i32.device.type == "cpu"
+                and images_u8.is_contiguous() and labels_u8.is_contiguous() and idx_i32.is_contiguous()
+                and images_u8.shape[0] == labels_u8.shape[0] and images_u8[0].numel() == 784):
+            raise ValueError("train_step_gather: expected contiguous host tensors uint8 [n,28,28] / uint8 [n] / int32 [batch]")
+        # indices are range-checked by the native side against the dataset size
         N.check(self.lib.b200_engine_train_step_gather(self.handle, images_u8.data_ptr(), labels_u8.data_ptr(),
-                                                       idx_i32.data_ptr(), int(idx_i32.numel()), int(use_graph),
-                                                       self._s()))
+                                                       int(images_u8.shape[0]), idx_i32.data_ptr(),
+                                                       int(idx_i32.numel()), int(use_graph), self._s()))
         self.steps += 1
         return self.steps - 1
 

@@ -383,3 +383,38 @@ def test_ranks_on_different_hosts_fall_back_to_nccl(monkeypatch, capsys):
     assert out.count("falling back from --comm auto to --comm nccl") == 1
     hosts[1] = "node-a"
     assert fused_ddp.FusedDataParallel(info, "twoshot")._single_host()
+
+
+def test_train_step_gather_validates_tensors_and_passes_the_dataset_size():
+    """The host gather indexes a raw pointer: the Python side checks dtype / device / layout, the native side checks
+    every index against the dataset size it is given (argument order = header = ctypes signature)."""
+    import re
+    from pytorch_mnist_ddp_b200 import _native as N
+    from pytorch_mnist_ddp_b200 import engine as E
+    calls = []
+
+    class Lib:
+        def b200_engine_train_step_gather(self, *a):
+            calls.append(a)
+            return 0
+
+    eng = E.NativeEngine.__new__(E.NativeEngine)
+    eng.lib, eng.handle, eng.steps, eng._s = Lib(), 1234, 0, (lambda: 0)
+    img = torch.zeros(50, 28, 28, dtype=torch.uint8)
+    lbl = torch.zeros(50, dtype=torch.uint8)
+    idx = torch.arange(8, dtype=torch.int32)
+    assert eng.train_step_gather(img, lbl, idx) == 0 and eng.steps == 1
+    sig = N._SIGNATURES["b200_engine_train_step_gather"]
+    assert len(calls[0]) == len(sig) == 8
+    assert calls[0][:4] == (1234, img.data_ptr(), lbl.data_ptr(), 50) and calls[0][4:7] == (idx.data_ptr(), 8, 1)
+    header = open(os.path.join(ROOT, "include", "b200mnist.h")).read()
+    decl = re.search(r"int b200_engine_train_step_gather\(([^;]*)\);", header).group(1)
+    names = [p.split()[-1].lstrip("*") for p in decl.replace("\n", " ").split(",")]
+    assert names == ["engine", "images_host", "labels_host", "n_samples", "idx_host", "batch", "use_graph", "stream"]
+    src = open(os.path.join(ROOT, "csrc", "engine.cu")).read()
+    assert "idx_host[b] >= 0 && idx_host[b] < n_samples" in src
+    for bad in [(img.to(torch.float32), lbl, idx), (img, lbl.to(torch.int64), idx), (img, lbl, idx.to(torch.int64)),
+                (img, lbl[:10], idx), (img.transpose(1, 2), lbl, idx), (img.view(50, 784)[:, :100], lbl, idx)]:
+        with pytest.raises(ValueError, match="train_step_gather"):
+            eng.train_step_gather(*bad)
+    assert len(calls) == 1
