@@ -208,6 +208,34 @@ def test_host_batch_step_equals_resident_step():
     a.close(); b.close()
 
 
+def test_gather_step_equals_resident_step_and_rejects_bad_indices():
+    """The data-loader entry point (native host gather -> pinned -> H2D -> step; what bench.py's e2e number times)
+    trains exactly like the resident path on the same sample order, in graph replay; an index outside the dataset is
+    an error before anything is read."""
+    from pytorch_mnist_ddp_b200 import _native as N
+    train, test = _data()
+    a, _ = _engine(train, test, use_tc=None)
+    b, _ = _engine(train, test, use_tc=None)
+    idx = torch.randperm(len(train))[:512].to(torch.int32)
+    a.begin_epoch(idx)
+    b.begin_epoch(None)
+    for step in range(8):  # steps 0/1 eager (one per staging slot), then captured graphs
+        sa = a.train_step(64)
+        sb = b.train_step_gather(train.images, train.labels, idx[step * 64: (step + 1) * 64].contiguous())
+        assert a.read_loss(sa) == b.read_loss(sb)
+    torch.cuda.synchronize()
+    assert torch.equal(a.params, b.params)
+    bad = idx[:64].clone()
+    bad[5] = len(train)
+    with pytest.raises(N.NativeError, match="outside the dataset"):
+        b.train_step_gather(train.images, train.labels, bad)
+    bad[5] = -1
+    with pytest.raises(N.NativeError, match="outside the dataset"):
+        b.train_step_gather(train.images, train.labels, bad)
+    assert b.steps == 8
+    a.close(); b.close()
+
+
 def test_dropout_is_deterministic_per_seed_and_differs_across_seeds():
     train, test = _data()
     outs = []
