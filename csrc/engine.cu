@@ -7,20 +7,21 @@
 // device-driven: sample cursor, step counter (dropout offset), lr and the loss ring live in a
 // device control block, so the host only enqueues "one more step" and never synchronises.
 //
-// Kernels of a step (single GPU, resident data).  Main stream = the critical path:
-//   conv1_fwd (gather+normalise+conv+ReLU) -> conv2_fwd (+bias+ReLU+pool+dropout)
-//   -> fc1 GEMM (split-K) -> head_fused (reduce+bias+ReLU+dropout, fc2, log_softmax, NLL, bwd seed)
-//   -> fc1 dgrad (+dropout/ReLU mask) -> un-pool -> conv2 dgrad (+ReLU mask) -> conv1 wgrad
-//   -> last kernel: conv-bucket partial reduction + Adadelta + step counter advance.
+// Kernels of a step (12 launches).  Main stream = the critical path:
+//   conv1+conv2 forward in ONE kernel (gather + normalise + conv1 + ReLU in the producer warps, conv2 on tcgen05,
+//   bias + ReLU + 2x2 max-pool + arg-max + dropout in the epilogue)
+//   -> fc1 GEMM (split-K) -> head_fused (partial sum + bias + ReLU + dropout, fc2, log_softmax, NLL, backward seed)
+//   -> fc1 dgrad (+dropout/ReLU mask) -> conv2 wgrad -> conv2 dgrad (both expand (pooled gradient, arg-max) on chip:
+//   the dense dY never exists) -> conv1 wgrad
+//   -> last kernel: conv-bucket Adadelta (+ conv1's partial rows) + step counter advance.
 // Branch 0 (forked after head_fused): head_wgrad -> fc1 wgrad -> [bucket 0 ready] fc-bucket Adadelta
 //   (waits for fc1 dgrad, which still reads the old fc1.weight).
-// Branch 1 (forked after un-pool): conv2 wgrad.
+// Branch 1 (forked after conv2 wgrad): conv2's per-CTA partial rows -> gradient (-> cross-GPU all-reduce).
 // Both branches are joined before the last kernel; forks and joins are events, so the whole step is
-// still ONE capturable graph.  With world > 1 the "bucket ready" point launches the fused
-// all-reduce+Adadelta kernel of allreduce.cu from branch 0 (it overlaps the conv backward) and the last
-// kernel is allreduce.cu's finalize_bucket_kernel.  Gradients are written straight into the flat
-// (symmetric) bucket: there is no bucket copy-in/copy-out and no zero_grad (every wgrad
-// kernel overwrites).
+// still ONE capturable graph.  With world > 1 the "bucket ready" points launch allreduce.cu's kernels instead:
+// fused_allreduce_kernel (+Adadelta) on branch 0, conv2_reduce_kernel on branch 1, conv_finalize_kernel as the last
+// kernel.  Gradients are written straight into the flat (symmetric) bucket: there is no bucket copy-in/copy-out
+//  and no zero_grad (every wgrad kernel overwrites).
 #include <cstdlib>
 #include <cstring>
 #include <map>

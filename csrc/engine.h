@@ -7,7 +7,7 @@
 #include "common.cuh"
 
 // which layers run on the tcgen05 kernels (B200EngineConfig.use_tc); a cleared bit selects the fp32 CUDA-core kernel
-enum { B200_TC_CONV2_FWD = 1 /* conv1+conv2 forward in one kernel (tc_conv2_v4.cu) */, B200_TC_FC1_FWD = 2,
+enum { B200_TC_CONV2_FWD = 1 /* conv1+conv2 forward in one kernel (tc_conv2_fwd.cu) */, B200_TC_FC1_FWD = 2,
        B200_TC_FC1_BWD = 4, B200_TC_CONV2_BWD = 8 /* dgrad + wgrad straight from (dp, argmax): no dense dY */,
        B200_TC_FC1_FP32 = 16 /* fc1 GEMMs as 3xTF32 split-operand products (fp32-class, the reference's SGEMM accuracy) */ };
 
