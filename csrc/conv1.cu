@@ -6,6 +6,8 @@
 //             ((x/255 - .1307)/.3081, mnist_ddp.py:153-156) + conv + bias + ReLU, one pass, NHWC out.
 //             Replaces the reference's DataLoader worker, H2D copy, cuDNN conv, bias add and ReLU
 //             kernels.
+//             The training step and evaluation run this inside the conv2 forward kernel (tc_conv2_fwd.cu, producer
+//             warps); the stand-alone kernel remains for the fp32 CUDA-core path (B200_TC bit 0 cleared) and as oracle.
 //   wgrad   : dW[tap][o] = sum da1 * x, db[o] = sum da1; input needs no gradient.
 #include <mutex>
 

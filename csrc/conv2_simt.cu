@@ -1,7 +1,7 @@
 // conv2 (32->64, 3x3) on CUDA cores: forward, dgrad and wgrad.
 //
 // These SIMT kernels are (a) the numerics oracle for the tcgen05 implicit-GEMM kernels in
-// tc_conv2.cu, and (b) the path used for shapes the tensor-core kernels do not take.  They fuse
+// tc_conv2_fwd.cu / tc_conv2_bwd.cu, and (b) the path used for shapes the tensor-core kernels do not take.  They fuse
 // the same epilogues/producers as the tensor-core versions so the surrounding buffers are
 // identical:
 //   forward : bias + ReLU + 2x2 max-pool (2-bit argmax) + dropout(.25)   (mnist_ddp.py:52-55)

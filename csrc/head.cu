@@ -1,6 +1,6 @@
 // Classifier head: everything after the fc1 GEMM, forward and backward, in two kernels.
 //
-// head_fused   (one warp per sample)
+// head_fused   (one warp per sample; four warps share a sample's split-K reduction when there are >= 8 partials)
 //     split-K reduce of the fc1 partials + bias + ReLU + dropout(.5)           (mnist_ddp.py:57-59)
 //     fc2 (128->10) + log_softmax + NLL                                        (mnist_ddp.py:60-61,71)
 //     backward seed: dlogits = (softmax - onehot)/B, dh = (dlogits . W2) * mask
