@@ -419,6 +419,12 @@ def run_ours(args) -> dict:
     return out if rank == 0 else {}
 
 
+def _self_launch_cmd(gpus: int, argv) -> list:
+    port = 29500 + os.getpid() % 2000
+    return [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={gpus}", "--master-addr",
+            "127.0.0.1", "--master-port", str(port), os.path.abspath(__file__), *argv]
+
+
 def main() -> None:
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -430,6 +436,9 @@ def main() -> None:
     ap.add_argument("--comm", default="auto")
     ap.add_argument("--no-graph", action="store_true")
     args = ap.parse_args()
+    if args.gpus > 1 and "WORLD_SIZE" not in os.environ:
+        # started by hand without a launcher: become the N-rank job the flag asks for (one process per GPU)
+        raise SystemExit(subprocess.call(_self_launch_cmd(args.gpus, sys.argv[1:])))
     if args.impl == "reference":
         from baseline.reference_arm import run_reference
         out = run_reference(args)

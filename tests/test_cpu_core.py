@@ -418,3 +418,24 @@ def test_train_step_gather_validates_tensors_and_passes_the_dataset_size():
         with pytest.raises(ValueError, match="train_step_gather"):
             eng.train_step_gather(*bad)
     assert len(calls) == 1
+
+
+def test_bench_launches_itself_under_torchrun_when_started_by_hand(monkeypatch):
+    """`python bench.py --gpus 4` without a launcher re-executes itself as 4 ranks on 127.0.0.1; under torchrun
+    (WORLD_SIZE set) it never does."""
+    import bench
+    seen = {}
+    monkeypatch.delenv("WORLD_SIZE", raising=False)
+    monkeypatch.setattr(sys, "argv", ["bench.py", "--gpus", "4", "--steps", "7", "--warmup", "3"])
+    monkeypatch.setattr(bench.subprocess, "call", lambda cmd: seen.setdefault("cmd", cmd) and 0)
+    with pytest.raises(SystemExit) as e:
+        bench.main()
+    assert e.value.code == 0
+    cmd = seen["cmd"]
+    assert cmd[1:4] == ["-m", "torch.distributed.run", "--nnodes=1"] and "--nproc-per-node=4" in cmd
+    assert cmd[cmd.index("--master-addr") + 1] == "127.0.0.1"
+    assert cmd[-6:] == ["--gpus", "4", "--steps", "7", "--warmup", "3"] and cmd[-7].endswith("bench.py")
+    monkeypatch.setenv("WORLD_SIZE", "4")
+    monkeypatch.setattr(bench, "run_ours", lambda args: seen.setdefault("ran", args.gpus) and None)
+    bench.main()
+    assert seen["ran"] == 4
