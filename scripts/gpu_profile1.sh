@@ -13,7 +13,7 @@ timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none --cache-co
 echo "launches rc=$?" >> $O/status.txt
 CMD2="python bench.py --steps 4 --warmup 3 --epochs 0 --no-graph"
 timeout 300 $CMD2 > $O/plain_eager.log 2>&1 &&
-timeout 900 ncu --set full --clock-control none --import-source on -s 36 -c 12 -f -o $O/step_full $CMD2 > $O/ncu_step.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -s 39 -c 13 -f -o $O/step_full $CMD2 > $O/ncu_step.log 2>&1
 echo "ncu step rc=$?" >> $O/status.txt
 CMD3="python bench.py --steps 4 --warmup 3 --epochs 0 --no-graph --comm twoshot"
 B200_FORCE_DDP=1 timeout 300 $CMD3 > $O/plain_ddp.log 2>&1 &&
