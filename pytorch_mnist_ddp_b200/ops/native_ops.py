@@ -7,7 +7,6 @@ training engine does not go through here — it sequences the same kernels in C+
 """
 from __future__ import annotations
 
-import ctypes
 from typing import Optional, Tuple
 
 import torch

@@ -4,7 +4,6 @@ Oracle = torch ops on the GPU with TF32 disabled (the reference trains convs in 
 fp32; the CUDA-core kernels here are full fp32, the tcgen05 ones TF32 — tolerances
 below reflect that).  Layout conversions are done here, never in the kernels under test.
 """
-import os
 
 import pytest
 import torch
