@@ -30,6 +30,7 @@ What is modelled (file:line = where the real thing is):
   conv_finalize_kernel    csrc/allreduce.cu  (conv2 CTAs poll the local flag; conv1 CTAs all-to-all barrier)
   step graph              csrc/engine.cu:enqueue_train (main stream, fc branch, conv2 branch, the joins)
   rank-0-only work between steps (evaluation / checkpoint: reads every parameter; mnist_ddp.py:183-189)
+  b200_comm_run back to back  (StandaloneModel: the stand-alone entry point, where the exit barrier IS needed)
 
 `mutate=` removes one ordering at a time; tests/test_protocol_model.py asserts that each removal is caught, which is
 what makes a clean result on the unmutated model mean something.
@@ -322,6 +323,50 @@ class StepModel:
             if nxt and not hb(i, nxt[0]):
                 raise Violation(f"early overwrite: {g.describe(nxt[0])} is not ordered after {g.describe(i)}")
         return {"events": len(g.kind), "waits": n_wait, "reads": n_read, "cells": len(writes), "slots": len(sigs)}
+
+
+class StandaloneModel(StepModel):
+    """`b200_comm_run` called back to back on one bucket (tests, benchmarks/allreduce_bench.py): the caller refills the
+    gradient buffer between calls, nothing else orders the ranks, so here the kernel's EXIT barrier is what keeps a
+    fast rank's refill away from a slow rank's loads.  Tokens grow by 2 per call; the exit barrier uses token + 1 on
+    the phase-1 slots."""
+
+    def __init__(self, world: int, calls: int, mode: int = TWOSHOT, exit_barrier: bool = True, ctas: int = 2) -> None:
+        self.W, self.S, self.fc_mode, self.fc_ctas, self.mut = world, calls, mode, ctas, None
+        self.exit_barrier = exit_barrier
+        self.g = Graph()
+        g, W = self.g, world
+        init = []
+        for r in range(W):
+            ops = [("W", ("P", r, o, b), 0) for o in range(W) for b in range(ctas)]
+            ops += [("W", ("G", r, o, b), 0) for o in range(W) for b in range(ctas)]
+            init.append(self.seq(r, "init", ops, ())[1])
+        start = g.add(0, "NOP", (), 0, "rendezvous", tuple(init))
+        last = [start] * W
+        for t in range(calls):
+            for r in range(W):
+                fill = self.kernel(r, f"call {t} fill gradients",
+                                   [[("W", ("G", r, o, b), t + 1) for o in range(W) for b in range(ctas)]], (last[r],))
+                last[r] = self.kernel(r, f"call {t} all-reduce", self._run(r, t), (fill,))
+
+    def _run(self, r: int, t: int):
+        W, tk = self.W, 2 * t + 1
+        ctas = []
+        for b in range(self.fc_ctas):
+            ops = [("SIG", ("p0", b, r, q), tk) for q in range(W)] + [("WAIT", ("p0", b, q, r), tk) for q in range(W)]
+            own = [r] if self.fc_mode == TWOSHOT else list(range(W))
+            for o in own:
+                ops += [("R", ("G", q, o, b), t + 1) for q in range(W)]
+                ops += [("W", ("P", q, o, b), t + 1) for q in (range(W) if self.fc_mode == TWOSHOT else [r])]
+            if self.exit_barrier:
+                ops += [("SIG", ("p1", b, r, q), tk + 1) for q in range(W)]
+                ops += [("WAIT", ("p1", b, q, r), tk + 1) for q in range(W)]
+            ctas.append(ops)
+        return ctas
+
+
+def verify_standalone(world: int, calls: int = 3, mode: int = TWOSHOT, exit_barrier: bool = True) -> Dict[str, int]:
+    return StandaloneModel(world, calls, mode, exit_barrier).check()
 
 
 def verify(world: int, steps: int = 3, fc_mode: int = TWOSHOT, conv2_mode: int = TWOSHOT, mutate: Optional[str] = None,

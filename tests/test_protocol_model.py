@@ -68,3 +68,14 @@ def test_a_cyclic_wait_is_a_deadlock():
     m.g = g
     with pytest.raises(pm.Violation, match="deadlock"):
         m.check()
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+@pytest.mark.parametrize("mode", [pm.ONESHOT, pm.TWOSHOT])
+def test_standalone_calls_need_the_exit_barrier(world, mode):
+    """Back-to-back `b200_comm_run` calls (tests, microbenchmark) have no finalize kernel between them: with the exit
+    barrier they are clean, without it a fast rank's next gradient fill races a slow rank's loads -- which is why the
+    stand-alone entry point keeps the barrier that the training step drops."""
+    assert pm.verify_standalone(world, calls=3, mode=mode)["waits"] > 0
+    with pytest.raises(pm.Violation, match="early overwrite"):
+        pm.verify_standalone(world, calls=3, mode=mode, exit_barrier=False)
