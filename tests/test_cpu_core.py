@@ -439,3 +439,72 @@ def test_bench_launches_itself_under_torchrun_when_started_by_hand(monkeypatch):
     monkeypatch.setattr(bench, "run_ours", lambda args: seen.setdefault("ran", args.gpus) and None)
     bench.main()
     assert seen["ran"] == 4
+
+
+def test_epoch_driver_contract_with_a_recording_backend(capsys):
+    """fit() against a backend that only records calls: 8 ranks x batch 200 gives 38 steps per epoch with a ragged
+    last batch of 100, only rank 0 logs / evaluates (mnist_ddp.py:76-79,183-186), the lr pushed after
+    each epoch follows StepLR(gamma=0.7) (mnist_ddp.py:177,189), and the printed sample counter is
+    world * batch_idx * len(batch) as in the reference."""
+    import argparse
+    from pytorch_mnist_ddp_b200 import trainer
+    from pytorch_mnist_ddp_b200.parallel.dist import DistInfo
+    from pytorch_mnist_ddp_b200.parallel.sampler import distributed_indices
+    from pytorch_mnist_ddp_b200.utils import data
+
+    class Recorder:
+        name = "recorder"
+
+        def __init__(self):
+            self.calls, self.lrs, self.epochs = [], [], []
+
+        def begin_epoch(self, idx):
+            self.epochs.append(idx.clone())
+            self.calls.append("begin")
+
+        def train_step(self, step, batch, want_loss=True):
+            self.calls.append(("step", step, want_loss))
+            return float(step) if want_loss else None
+
+        def loss(self, token):
+            return 2.0 + token / 100.0
+
+        def evaluate(self, split, batch):
+            self.calls.append(("eval", len(split), batch))
+            return 2.3 * len(split), 1000
+
+        def set_lr(self, lr):
+            self.lrs.append(lr)
+
+        def finish(self):
+            self.calls.append("finish")
+
+    train, test = data.synthetic_split(True, 60000), data.synthetic_split(False, 10000)
+    args = argparse.Namespace(batch_size=200, test_batch_size=1000, epochs=3, lr=1.0, gamma=0.7, dry_run=False,
+                              log_interval=10)
+    for rank in (0, 3):
+        rec = Recorder()
+        info = DistInfo(distributed=True, rank=rank, world_size=8, gpu=rank)
+        stats = trainer.fit(args, rec, train, test, info, sampler_mode="distributed")
+        out = capsys.readouterr().out
+        steps = [c for c in rec.calls if isinstance(c, tuple) and c[0] == "step"]
+        assert stats["steps"] == len(steps) == 3 * 38
+        assert [c for c in rec.calls if c == "begin"] == ["begin"] * 3 and rec.calls[-1] == "finish"
+        assert all(torch.equal(e, distributed_indices(60000, 8, rank, k + 1)) for k, e in enumerate(rec.epochs))
+        assert rec.lrs == pytest.approx([0.7, 0.49, 0.343])
+        evals = [c for c in rec.calls if isinstance(c, tuple) and c[0] == "eval"]
+        if rank == 0:
+            assert evals == [("eval", 10000, 1000)] * 3 and out.count("Test set: Average loss: 2.3000") == 3
+            assert [s[1] for s in steps if s[2]] == [0, 10, 20, 30] * 3
+            lines = [l for l in out.splitlines() if l.startswith("Train Epoch")]
+            assert len(lines) == 12
+            assert lines[1] == "Train Epoch: 1 [16000/60000 (26%)]\tLoss: 2.100000"   # 8 * 10 * 200, 100*10/38
+            assert lines[3].startswith("Train Epoch: 1 [48000/60000 (79%)]")
+        else:
+            assert evals == [] and out == "" and not any(s[2] for s in steps)
+    # --eval-all-ranks: every rank evaluates, still only rank 0 prints
+    rec = Recorder()
+    trainer.fit(args, rec, train, test, DistInfo(distributed=True, rank=3, world_size=8, gpu=3),
+                sampler_mode="distributed", eval_all_ranks=True)
+    assert len([c for c in rec.calls if isinstance(c, tuple) and c[0] == "eval"]) == 3
+    assert capsys.readouterr().out == ""
