@@ -24,6 +24,8 @@ enum { B200_OK = 0, B200_ERR_ARG = -1, B200_ERR_CUDA = -2, B200_ERR_STATE = -3, 
 /* ---- runtime ------------------------------------------------------------------------------ */
 const char* b200_last_error(void);
 int b200_version(void);
+/* 1 when the library was built with the tcgen05 kernels (always, for sm_100a) */
+int b200_has_tc(void);
 /* number of kernels this library has launched in this process (graph replays included) */
 long long b200_launch_count(void);
 /* write the device control block (struct B200Ctrl in csrc/common.cuh) asynchronously */

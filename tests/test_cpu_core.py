@@ -508,3 +508,29 @@ def test_epoch_driver_contract_with_a_recording_backend(capsys):
                 sampler_mode="distributed", eval_all_ranks=True)
     assert len([c for c in rec.calls if isinstance(c, tuple) and c[0] == "eval"]) == 3
     assert capsys.readouterr().out == ""
+
+
+def test_c_abi_header_exports_and_ctypes_signatures_agree():
+    """include/b200mnist.h is the contract: every exported b200_* symbol is declared there, every declaration is
+    exported, every function that takes arguments has a ctypes signature with the same number of parameters, and the
+    header compiles as plain C."""
+    import re
+    import shutil
+    from pytorch_mnist_ddp_b200 import _native as N
+    path = N.build()
+    out = subprocess.run(["nm", "-D", "--defined-only", path], capture_output=True, text=True, check=True).stdout
+    exported = {l.split()[-1] for l in out.splitlines() if " T b200_" in l}
+    header = open(os.path.join(ROOT, "include", "b200mnist.h")).read()
+    header = re.sub(r"/\*.*?\*/", "", header, flags=re.S)
+    decls = {m.group(1): m.group(2) for m in re.finditer(r"\b(b200_[a-z0-9_]+)\s*\(([^;{]*)\)\s*;", header)}
+    assert exported == set(decls), (sorted(exported - set(decls)), sorted(set(decls) - exported))
+    for name, params in decls.items():
+        n = 0 if params.strip() in ("", "void") else params.count(",") + 1
+        if n:
+            assert name in N._SIGNATURES, f"{name} takes {n} arguments but has no ctypes signature"
+            assert len(N._SIGNATURES[name]) == n, (name, n, len(N._SIGNATURES[name]))
+    assert set(N._SIGNATURES) <= exported
+    if shutil.which("gcc"):
+        res = subprocess.run(["gcc", "-std=c99", "-pedantic", "-Werror", "-fsyntax-only", "-x", "c",
+                              os.path.join(ROOT, "include", "b200mnist.h")], capture_output=True, text=True)
+        assert res.returncode == 0, res.stderr
