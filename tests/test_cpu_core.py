@@ -530,6 +530,28 @@ def test_c_abi_header_exports_and_ctypes_signatures_agree():
             assert name in N._SIGNATURES, f"{name} takes {n} arguments but has no ctypes signature"
             assert len(N._SIGNATURES[name]) == n, (name, n, len(N._SIGNATURES[name]))
     assert set(N._SIGNATURES) <= exported
+
+    # ... and with the same parameter classes (an int passed where the callee reads a size_t is a silent bug on x86-64)
+    import ctypes
+    c_class = {"int": "i32", "unsigned int": "u32", "unsigned": "u32", "float": "f32", "double": "f64", "size_t": "u64",
+               "unsigned long long": "u64", "uint64_t": "u64", "long long": "i64", "uint32_t": "u32"}
+    ct_class = {ctypes.c_int: "i32", ctypes.c_uint: "u32", ctypes.c_float: "f32", ctypes.c_double: "f64",
+                ctypes.c_size_t: "u64", ctypes.c_ulonglong: "u64", ctypes.c_longlong: "i64"}
+
+    def of_c(param):
+        if "*" in param:
+            return "ptr"
+        return c_class[re.sub(r"\b[A-Za-z_][A-Za-z0-9_]*$", "", param.strip()).replace("const", "").strip()]
+
+    def of_ct(t):
+        if t in (ctypes.c_void_p, ctypes.c_char_p) or issubclass(t, ctypes._Pointer):
+            return "ptr"
+        return ct_class[t]
+
+    for name, params in decls.items():
+        if params.strip() not in ("", "void"):
+            want = [of_c(p) for p in params.replace("\n", " ").split(",")]
+            assert [of_ct(t) for t in N._SIGNATURES[name]] == want, name
     if shutil.which("gcc"):
         res = subprocess.run(["gcc", "-std=c99", "-pedantic", "-Werror", "-fsyntax-only", "-x", "c",
                               os.path.join(ROOT, "include", "b200mnist.h")], capture_output=True, text=True)
