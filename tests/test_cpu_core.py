@@ -534,9 +534,9 @@ def test_c_abi_header_exports_and_ctypes_signatures_agree():
     # ... and with the same parameter classes (an int passed where the callee reads a size_t is a silent bug on x86-64)
     import ctypes
     c_class = {"int": "i32", "unsigned int": "u32", "unsigned": "u32", "float": "f32", "double": "f64", "size_t": "u64",
-               "unsigned long long": "u64", "uint64_t": "u64", "long long": "i64", "uint32_t": "u32"}
+               "unsigned long long": "u64", "uint64_t": "u64", "long long": "i64", "long": "i64", "uint32_t": "u32"}
     ct_class = {ctypes.c_int: "i32", ctypes.c_uint: "u32", ctypes.c_float: "f32", ctypes.c_double: "f64",
-                ctypes.c_size_t: "u64", ctypes.c_ulonglong: "u64", ctypes.c_longlong: "i64"}
+                ctypes.c_size_t: "u64", ctypes.c_ulonglong: "u64", ctypes.c_longlong: "i64", ctypes.c_long: "i64"}
 
     def of_c(param):
         if "*" in param:
