@@ -556,3 +556,25 @@ def test_c_abi_header_exports_and_ctypes_signatures_agree():
         res = subprocess.run(["gcc", "-std=c99", "-pedantic", "-Werror", "-fsyntax-only", "-x", "c",
                               os.path.join(ROOT, "include", "b200mnist.h")], capture_output=True, text=True)
         assert res.returncode == 0, res.stderr
+
+
+@pytest.mark.skipif(__import__("shutil").which("gcc") is None, reason="needs a C compiler")
+def test_engine_config_struct_layout_matches_the_header(tmp_path):
+    """ctypes' EngineConfig must be laid out exactly like `B200EngineConfig` in include/b200mnist.h: compile a C
+    program that prints sizeof / offsetof of every field and compare."""
+    import ctypes
+    from pytorch_mnist_ddp_b200 import _native as N
+    fields = [f[0] for f in N.EngineConfig._fields_]
+    src = tmp_path / "layout.c"
+    src.write_text('#include <stdio.h>\n#include <stddef.h>\n#include "b200mnist.h"\nint main(void) {\n'
+                   '  printf("%zu\\n", sizeof(B200EngineConfig));\n'
+                   + "".join(f'  printf("{f} %zu\\n", offsetof(B200EngineConfig, {f}));\n' for f in fields)
+                   + "  return 0;\n}\n")
+    exe = tmp_path / "layout"
+    subprocess.run(["gcc", "-std=c99", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)], check=True)
+    out = subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.split("\n")
+    assert int(out[0]) == ctypes.sizeof(N.EngineConfig)
+    for line in out[1:]:
+        if line:
+            name, off = line.split()
+            assert getattr(N.EngineConfig, name).offset == int(off), name
