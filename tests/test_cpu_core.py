@@ -578,3 +578,27 @@ def test_engine_config_struct_layout_matches_the_header(tmp_path):
         if line:
             name, off = line.split()
             assert getattr(N.EngineConfig, name).offset == int(off), name
+
+
+@pytest.mark.skipif(__import__("shutil").which("gcc") is None, reason="needs a C compiler")
+def test_python_constants_match_the_header_enums(tmp_path):
+    """Buffer ids, the loss-ring length and the tensor-core mask bits are restated in Python: keep them equal to the C side."""
+    import re
+    from pytorch_mnist_ddp_b200 import engine as E
+    names = ["PARAMS", "GRADS0", "GRADS1", "SQ_AVG", "ACC_DELTA", "A1", "POOLED", "AMAX", "H", "DLOGITS", "DH", "DP", "DA1",
+             "LOSS_I", "LOSS_RING", "CTRL", "LOGP", "STAGE_IMG", "STAGE_LBL", "FC1_PART"]
+    src = tmp_path / "enums.c"
+    src.write_text('#include <stdio.h>\n#include "b200mnist.h"\nint main(void) {\n'
+                   + "".join(f'  printf("{n} %d\\n", (int)B200_BUF_{n});\n' for n in names)
+                   + '  printf("RING %d\\n", (int)B200_LOSS_RING);\n  return 0;\n}\n')
+    exe = tmp_path / "enums"
+    subprocess.run(["gcc", "-std=c99", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)], check=True)
+    vals = dict(l.split() for l in subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.splitlines())
+    for n in names:
+        assert getattr(E, "BUF_" + n) == int(vals[n]), n
+    assert E.LOSS_RING == int(vals["RING"])
+    eh = open(os.path.join(ROOT, "csrc", "engine.h")).read()
+    bits = {m.group(1): int(m.group(2)) for m in re.finditer(r"B200_TC_([A-Z0-9_]+) = (\d+)", eh)}
+    assert bits == {"CONV2_FWD": E.TC_CONV2_FWD, "FC1_FWD": E.TC_FC1_FWD, "FC1_BWD": E.TC_FC1_BWD,
+                    "CONV2_BWD": E.TC_CONV2_BWD, "FC1_FP32": E.TC_FC1_FP32}
+    assert E.DEFAULT_TC == 31
